@@ -1,0 +1,321 @@
+// 3x3 / stride 1 / pad 1 convolution as an implicit GEMM on the 5th-gen tensor cores (tcgen05, kind::tf32, fp32
+// accumulation in TMEM), operands staged by TMA.  One kernel template covers the three GEMMs of a conv layer:
+//
+//   FPROP  D[pix, co] = sum_{tap,ci} X[pix+tap, ci] * W[co, tap, ci]      A: K-major (4-D TMA box, halo = OOB zero fill)
+//                                                                         B: K-major (weights are KRSC, ci contiguous)
+//   DGRAD  D[pix, ci] = sum_{tap,co} dY[pix+tap, co] * W[co, 8-tap, ci]   A: K-major, B: MN-major (same KRSC weights,
+//                                                                         no repacked copy)
+//   WGRAD  D[co, ci]  = sum_pix dY[pix, co] * X[pix+tap, ci]  (per tap)   A: MN-major, B: MN-major, K = pixels
+//
+// Replaces what the reference reaches through aten::(mkldnn_)convolution / convolution_backward
+// (reference model.py:18-23).
+//
+// Tile: 128 (M) x NT (N) per CTA, K consumed in chunks of 32 tf32 (one 128-byte swizzle row), 4 UMMA k-steps of 8.
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer, warps 2..5 =
+// epilogue (TMEM -> registers -> smem transpose -> coalesced 128-byte global rows).
+// Split-K: every split writes its fp32 partial tile to a workspace; the CTA that arrives last on the tile's counter
+// reduces the partials in split order (deterministic), applies the bias and emits the per-channel sum / sum-of-squares
+// partials that the BatchNorm finalize kernel consumes.
+#pragma once
+#include <cuda.h>
+#include "ptx.cuh"
+
+namespace dpb {
+
+enum ConvGemmMode : int { kFprop = 0, kDgrad = 1, kWgrad = 2 };
+
+struct ConvGemmParams {
+  int H, W, NImg;        // activation geometry (input == output spatial size)
+  int Ck;                // channels along GEMM-K for fprop/dgrad (Cin for fprop, Cout for dgrad); unused for wgrad
+  int CinW;              // Cin of the weight tensor (row pitch of KRSC = 9*CinW)
+  int M_total, N_total;  // GEMM extents: fprop/dgrad M = pixels; wgrad M = Cout.  N = channels of the output columns
+  int k_iters;           // total K iterations of 32: fprop/dgrad 9*Ck/32; wgrad ceil(pixels/32)
+  int splits;            // split-K factor (>=1)
+  int box_w, box_h, box_n;  // pixel box of one A tile (fprop/dgrad: 128 pixels) or one K chunk (wgrad: 32 pixels)
+  float* out;            // fprop: Y[pix][Cout]; dgrad: dX[pix][Cin]; wgrad: dW[Cout][9][Cin]
+  long long out_ld;      // row pitch of `out` in floats
+  const float* bias;     // fprop only (may be null)
+  float* stat_sum;       // fprop only: [m_tiles][N_total] partial sums (may be null)
+  float* stat_sq;        // fprop only: [m_tiles][N_total]
+  float* workspace;      // split-K partials: [tiles][splits][128*NT]
+  unsigned int* counters;  // split-K arrival counters, one per tile, self-resetting
+};
+
+template <int NT, int STAGES>
+struct ConvGemmSmem {
+  static constexpr int kABytes = 128 * 128;  // 128 rows x 32 tf32
+  static constexpr int kBBytes = NT * 128;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStagingBytes = 4 * 32 * 33 * 4;  // per-epilogue-warp 32x33 fp32 transpose tile
+  static constexpr int kBarBytes = 256;
+  static constexpr int kTotal = 1024 /*align slack*/ + STAGES * kStageBytes + kStagingBytes + kBarBytes + 2 * NT * 4 * 4;
+};
+
+template <int MODE, int NT, int STAGES>
+__global__ void __launch_bounds__(192, 1)
+conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+                 const ConvGemmParams p) {
+  constexpr bool A_MN = (MODE == kWgrad);
+  constexpr bool B_MN = (MODE != kFprop);
+  using S = ConvGemmSmem<NT, STAGES>;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* stage_base = smem;
+  float* staging = reinterpret_cast<float*>(smem + STAGES * S::kStageBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * S::kStageBytes + S::kStagingBytes);
+  uint64_t* full_bar = bars;               // [STAGES]
+  uint64_t* empty_bar = bars + STAGES;     // [STAGES]
+  uint64_t* acc_bar = bars + 2 * STAGES;   // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
+  uint32_t* last_flag = tmem_slot + 1;
+  float* colred = reinterpret_cast<float*>(smem + STAGES * S::kStageBytes + S::kStagingBytes + S::kBarBytes);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int m_tile = blockIdx.x;
+  const int n_tile = blockIdx.y;
+  // blockIdx.z = tap * splits + split for wgrad, = split otherwise
+  const int split = (MODE == kWgrad) ? (blockIdx.z % p.splits) : blockIdx.z;
+  const int wtap = (MODE == kWgrad) ? (blockIdx.z / p.splits) : 0;
+
+  // K range of this split (balanced, contiguous)
+  const int kq = p.k_iters / p.splits, kr = p.k_iters % p.splits;
+  const int k_begin = split * kq + min(split, kr);
+  const int k_count = kq + (split < kr ? 1 : 0);
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&mapA);
+    tma_prefetch_desc(&mapB);
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(acc_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<NT>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_acc = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (elect_one()) {
+      int a_w0 = 0, a_h0 = 0, a_n0 = 0;
+      if (MODE != kWgrad) {
+        // pixel box of this M tile
+        const int tiles_w = p.W / p.box_w;  // box_w divides W by construction
+        const int tiles_h = p.H / p.box_h;
+        int t = m_tile;
+        a_w0 = (t % tiles_w) * p.box_w; t /= tiles_w;
+        a_h0 = (t % tiles_h) * p.box_h; t /= tiles_h;
+        a_n0 = t * p.box_n;
+      }
+      const int cpt = (MODE != kWgrad) ? (p.Ck >> 5) : 1;  // 32-channel chunks per tap
+      for (int i = 0; i < k_count; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1, 100 + s);
+        uint8_t* sa = stage_base + s * S::kStageBytes;
+        uint8_t* sb = sa + S::kABytes;
+        mbar_arrive_expect_tx(&full_bar[s], S::kStageBytes);
+        const int kk = k_begin + i;
+        if (MODE == kFprop) {
+          const int tap = kk / cpt, cc = kk - tap * cpt;
+          const int r = tap / 3, sx = tap - 3 * r;
+          tma_load_4d(sa, &mapA, &full_bar[s], cc * 32, a_w0 + sx - 1, a_h0 + r - 1, a_n0);
+          tma_load_2d(sb, &mapB, &full_bar[s], tap * p.CinW + cc * 32, n_tile * NT);
+        } else if (MODE == kDgrad) {
+          const int tap = kk / cpt, cc = kk - tap * cpt;
+          const int r = tap / 3, sx = tap - 3 * r;
+          tma_load_4d(sa, &mapA, &full_bar[s], cc * 32, a_w0 + sx - 1, a_h0 + r - 1, a_n0);
+          // weights viewed as (ci%32, co, (tap*Cin+ci)/32): rows = co (GEMM K), 128-byte row = 32 ci (GEMM N)
+          tma_load_3d(sb, &mapB, &full_bar[s], 0, cc * 32, ((8 - tap) * p.CinW + n_tile * NT) >> 5);
+        } else {
+          const int r = wtap / 3, sx = wtap - 3 * r;
+          const int p0 = kk * 32;
+          const int w0 = p0 % p.W;
+          const int h0 = (p0 / p.W) % p.H;
+          const int n0 = p0 / (p.W * p.H);
+          // dY viewed as (co%32, pix, co/32)
+          tma_load_3d(sa, &mapA, &full_bar[s], 0, p0, m_tile * 4);
+          // X viewed as (ci%32, w, h, n, ci/32)
+          tma_load_5d(sb, &mapB, &full_bar[s], 0, w0 + sx - 1, h0 + r - 1, n0, n_tile * (NT / 32));
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    constexpr uint32_t idesc = umma_idesc_tf32(NT, A_MN, B_MN);
+    // K-major SW128: 8-row groups 1024 B apart (SBO), LBO unused.  MN-major SW128: 32-element MN atoms are one
+    // 32-row x 128 B block (4096 B) apart (LBO), 8-row K groups 1024 B apart (SBO).
+    constexpr uint32_t a_lbo = A_MN ? 4096 : 16, a_sbo = 1024;
+    constexpr uint32_t b_lbo = B_MN ? 4096 : 16, b_sbo = 1024;
+    constexpr uint32_t a_kstep = A_MN ? 1024 : 32;  // bytes per UMMA k-step (8 tf32)
+    constexpr uint32_t b_kstep = B_MN ? 1024 : 32;
+    for (int i = 0; i < k_count; ++i) {
+      const int s = i % STAGES;
+      const uint32_t ph = (i / STAGES) & 1;
+      mbar_wait(&full_bar[s], ph, 200 + s);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t sa = smem_u32(stage_base + s * S::kStageBytes);
+        const uint32_t sb = sa + S::kABytes;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+          const uint64_t ad = umma_smem_desc_sw128(sa + ks * a_kstep, a_lbo, a_sbo);
+          const uint64_t bd = umma_smem_desc_sw128(sb + ks * b_kstep, b_lbo, b_sbo);
+          umma_tf32(tmem_acc, ad, bd, idesc, (i > 0 || ks > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);              // frees the smem slot when these MMAs retire
+        if (i == k_count - 1) umma_commit(acc_bar);  // accumulator complete
+      }
+      __syncwarp();
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps (2..5)
+    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    float* tile = staging + q * (32 * 33);
+    const int row_base = m_tile * 128 + q * 32;
+    const int tile_id = ((MODE == kWgrad ? wtap : 0) * gridDim.y + n_tile) * gridDim.x + m_tile;
+    float* ws = nullptr;
+    if (p.splits > 1) ws = p.workspace + ((size_t)tile_id * p.splits + split) * (size_t)(128 * NT);
+
+    if (k_count > 0) {
+      mbar_wait(acc_bar, 0, 300);
+      tc_fence_after();
+    }
+    float csum = 0.f, csq = 0.f;
+#pragma unroll 1
+    for (int c0 = 0; c0 < NT; c0 += 32) {
+      float v[32];
+      if (k_count > 0) {
+        tmem_ld_32x32(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = v[j];
+      __syncwarp();
+      const int col = n_tile * NT + c0 + lane;
+      if (p.splits > 1) {
+#pragma unroll 4
+        for (int i = 0; i < 32; ++i) ws[(size_t)(q * 32 + i) * NT + c0 + lane] = tile[i * 33 + lane];
+      } else {
+        float b = 0.f;
+        if (MODE == kFprop && p.bias != nullptr) b = p.bias[col];
+        float* orow;
+        if (MODE == kWgrad)
+          orow = p.out + (size_t)row_base * p.out_ld + (size_t)wtap * p.CinW + col;
+        else
+          orow = p.out + (size_t)row_base * p.out_ld + col;
+        csum = 0.f; csq = 0.f;
+#pragma unroll 4
+        for (int i = 0; i < 32; ++i) {
+          if (row_base + i < p.M_total) {
+            const float y = tile[i * 33 + lane] + b;
+            orow[(size_t)i * p.out_ld] = y;
+            csum += y;
+            csq += y * y;
+          }
+        }
+        if (MODE == kFprop && p.stat_sum != nullptr) {
+          colred[(q * 2 + 0) * NT + c0 + lane] = csum;
+          colred[(q * 2 + 1) * NT + c0 + lane] = csq;
+        }
+      }
+      __syncwarp();
+    }
+    tc_fence_before();
+    // named barrier over the 128 epilogue threads
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    const int et = threadIdx.x - 64;  // 0..127
+    if (p.splits == 1) {
+      if (MODE == kFprop && p.stat_sum != nullptr) {
+        for (int c = et; c < NT; c += 128) {
+          float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            s0 += colred[(w * 2 + 0) * NT + c];
+            s1 += colred[(w * 2 + 1) * NT + c];
+          }
+          p.stat_sum[(size_t)m_tile * p.N_total + n_tile * NT + c] = s0;
+          p.stat_sq[(size_t)m_tile * p.N_total + n_tile * NT + c] = s1;
+        }
+      }
+    } else {
+      // split-K: publish partial, last arriver reduces
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (et == 0) {
+        const unsigned int old = atomicAdd(&p.counters[tile_id], 1u);
+        *last_flag = (old == (unsigned)p.splits - 1) ? 1u : 0u;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (*last_flag) {
+        __threadfence();
+        const float* wsb = p.workspace + (size_t)tile_id * p.splits * (size_t)(128 * NT);
+        constexpr int C4 = NT / 4;          // float4 columns per row
+        constexpr int RG = 128 / C4 > 0 ? 128 / C4 : 1;  // row groups covered by the 128 threads at once
+        const int c4 = et % C4;
+        const int rg = et / C4;
+        float4 ssum = make_float4(0.f, 0.f, 0.f, 0.f), ssq = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int colb = n_tile * NT + c4 * 4;
+        if (MODE == kFprop && p.bias != nullptr) b4 = *reinterpret_cast<const float4*>(p.bias + colb);
+        if (rg < RG) {
+          for (int r = rg; r < 128; r += RG) {
+            const int grow = m_tile * 128 + r;
+            if (grow >= p.M_total) break;
+            float4 acc = b4;
+            for (int sp = 0; sp < p.splits; ++sp) {
+              const float4 t = __ldcg(reinterpret_cast<const float4*>(wsb + (size_t)sp * (128 * NT) + (size_t)r * NT) + c4);
+              acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+            }
+            float* orow;
+            if (MODE == kWgrad)
+              orow = p.out + (size_t)grow * p.out_ld + (size_t)wtap * p.CinW + colb;
+            else
+              orow = p.out + (size_t)grow * p.out_ld + colb;
+            *reinterpret_cast<float4*>(orow) = acc;
+            ssum.x += acc.x; ssum.y += acc.y; ssum.z += acc.z; ssum.w += acc.w;
+            ssq.x += acc.x * acc.x; ssq.y += acc.y * acc.y; ssq.z += acc.z * acc.z; ssq.w += acc.w * acc.w;
+          }
+        }
+        if (MODE == kFprop && p.stat_sum != nullptr) {
+          // reduce the RG row groups per column through smem (staging is free now: 4*32*33 floats >= 2*128*4... )
+          float* red = staging;  // [RG][2][NT]
+          if (rg < RG) {
+            *reinterpret_cast<float4*>(red + ((size_t)rg * 2 + 0) * NT + c4 * 4) = ssum;
+            *reinterpret_cast<float4*>(red + ((size_t)rg * 2 + 1) * NT + c4 * 4) = ssq;
+          }
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          for (int c = et; c < NT; c += 128) {
+            float s0 = 0.f, s1 = 0.f;
+            for (int g = 0; g < RG; ++g) {
+              s0 += red[((size_t)g * 2 + 0) * NT + c];
+              s1 += red[((size_t)g * 2 + 1) * NT + c];
+            }
+            p.stat_sum[(size_t)m_tile * p.N_total + n_tile * NT + c] = s0;
+            p.stat_sq[(size_t)m_tile * p.N_total + n_tile * NT + c] = s1;
+          }
+        }
+        if (et == 0) p.counters[tile_id] = 0u;  // re-arm for the next launch (graph replays included)
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<NT>(tmem_acc);
+  }
+}
+
+}  // namespace dpb

@@ -1,0 +1,189 @@
+// Host side of the tcgen05 implicit-GEMM convolution: TMA tensor-map construction (driver entry point fetched at
+// run time, so the library links without libcuda) and launch heuristics (N tile, split-K factor).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <mutex>
+#include "conv_gemm.cuh"
+#include "errors.cuh"
+
+namespace dpb {
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+inline PFN_encodeTiled get_encode_tiled() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres);
+    if (e == cudaSuccess && qres == cudaDriverEntryPointSuccess) fn = reinterpret_cast<PFN_encodeTiled>(sym);
+  });
+  return fn;
+}
+
+// fp32 tensor map, SWIZZLE_128B, zero fill out of bounds.  dims/strides innermost first; strides[i] is the byte pitch
+// of dimension i+1.
+inline int make_map_f32(CUtensorMap* map, const void* base, int rank, const cuuint64_t* dims,
+                        const cuuint64_t* strides_bytes, const cuuint32_t* box) {
+  PFN_encodeTiled enc = get_encode_tiled();
+  if (!enc) return set_error(-10, "cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(base), dims,
+                   strides_bytes, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(-11, "cuTensorMapEncodeTiled failed (rank %d, CUresult %d)", rank, (int)r);
+  return 0;
+}
+
+struct ConvGeom {
+  int n, h, w, cin, cout;
+};
+
+inline void pixel_box(int h, int w, int pixels, int* bw, int* bh, int* bn) {
+  *bw = w < pixels ? w : pixels;
+  int rest = pixels / *bw;
+  *bh = h < rest ? h : rest;
+  *bn = rest / *bh;
+}
+
+template <int MODE, int NT>
+int launch_conv_gemm_nt(const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
+                        cudaStream_t stream) {
+  constexpr int STAGES = (NT == 256) ? 4 : 4;
+  using S = ConvGemmSmem<NT, STAGES>;
+  auto kern = conv_gemm_kernel<MODE, NT, STAGES>;
+  static bool attr_set = false;  // per instantiation
+  if (!attr_set) {
+    DPB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+    attr_set = true;
+  }
+  kern<<<grid, 192, S::kTotal, stream>>>(mA, mB, p);
+  DPB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <int MODE>
+int launch_conv_gemm_mode(int nt, const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
+                          cudaStream_t stream) {
+  switch (nt) {
+    case 64: return launch_conv_gemm_nt<MODE, 64>(mA, mB, p, grid, stream);
+    case 128: return launch_conv_gemm_nt<MODE, 128>(mA, mB, p, grid, stream);
+    case 256: return launch_conv_gemm_nt<MODE, 256>(mA, mB, p, grid, stream);
+  }
+  return set_error(-12, "unsupported N tile %d", nt);
+}
+
+constexpr size_t kConvWorkspaceBytes = (size_t)48 << 20;  // split-K partial tiles
+constexpr int kConvCounterSlots = 8192;
+
+// Number of CTAs we aim for: two waves of single-tile CTAs on 148 SMs.
+constexpr int kTargetCtas = 296;
+
+inline int pick_splits(int tiles, int k_iters, int nt, int forced) {
+  int splits = 1;
+  if (forced > 0) {
+    splits = forced;
+  } else if (tiles < kTargetCtas) {
+    splits = kTargetCtas / tiles;
+    int max_by_k = k_iters / 4;  // keep >= 4 k-iterations (128 of K) per split
+    if (max_by_k < 1) max_by_k = 1;
+    if (splits > max_by_k) splits = max_by_k;
+  }
+  if (splits > k_iters) splits = k_iters;
+  if (splits < 1) splits = 1;
+  // workspace bound
+  while (splits > 1 && (size_t)tiles * splits * 128 * nt * 4 > kConvWorkspaceBytes) --splits;
+  return splits;
+}
+
+// mode: 0 fprop  (in = X[N,H,W,Cin], w = W[Cout,3,3,Cin], out = Y[N,H,W,Cout])
+//       1 dgrad  (in = dY[N,H,W,Cout], w = W, out = dX[N,H,W,Cin])
+//       2 wgrad  (in = dY[N,H,W,Cout], in2 = X[N,H,W,Cin], out = dW[Cout,3,3,Cin])
+inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, const float* in2, const float* w,
+                              float* out, const float* bias, float* stat_sum, float* stat_sq, float* workspace,
+                              unsigned int* counters, int nt_override, int splits_override, int* out_m_tiles,
+                              cudaStream_t stream) {
+  if (g.cin % 32 || g.cout % 32) return set_error(-13, "conv_gemm needs Cin, Cout multiples of 32 (got %d, %d)", g.cin, g.cout);
+  if (g.w > 32 || (g.w & (g.w - 1)) || (g.h & (g.h - 1))) return set_error(-13, "conv_gemm needs power-of-two H, W with W <= 32 (got %d x %d)", g.h, g.w);
+  const long long pixels = (long long)g.n * g.h * g.w;
+  ConvGemmParams p{};
+  p.H = g.h; p.W = g.w; p.NImg = g.n; p.CinW = g.cin;
+  p.bias = bias; p.stat_sum = stat_sum; p.stat_sq = stat_sq; p.workspace = workspace; p.counters = counters;
+  p.out = out;
+  CUtensorMap mA, mB;
+  dim3 grid;
+  int nt;
+  int rc;
+  if (mode == kFprop || mode == kDgrad) {
+    const int ck = (mode == kFprop) ? g.cin : g.cout;   // GEMM K channels
+    const int cn = (mode == kFprop) ? g.cout : g.cin;   // GEMM N channels
+    nt = nt_override > 0 ? nt_override : (cn >= 128 ? 128 : 64);
+    if (cn % nt) return set_error(-13, "N tile %d does not divide %d", nt, cn);
+    int bw, bh, bn;
+    pixel_box(g.h, g.w, 128, &bw, &bh, &bn);
+    p.box_w = bw; p.box_h = bh; p.box_n = bn;
+    p.Ck = ck;
+    p.M_total = (int)pixels; p.N_total = cn;
+    p.k_iters = 9 * (ck / 32);
+    p.out_ld = cn;
+    const int m_tiles = (int)((pixels + 127) / 128);
+    const int n_tiles = cn / nt;
+    p.splits = pick_splits(m_tiles * n_tiles, p.k_iters, nt, splits_override);
+    if (m_tiles * n_tiles > kConvCounterSlots && p.splits > 1) p.splits = 1;
+    {
+      cuuint64_t dims[4] = {(cuuint64_t)ck, (cuuint64_t)g.w, (cuuint64_t)g.h, (cuuint64_t)g.n};
+      cuuint64_t str[3] = {(cuuint64_t)ck * 4, (cuuint64_t)g.w * ck * 4, (cuuint64_t)g.h * g.w * ck * 4};
+      cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
+      if ((rc = make_map_f32(&mA, in, 4, dims, str, box))) return rc;
+    }
+    if (mode == kFprop) {
+      cuuint64_t dims[2] = {(cuuint64_t)9 * g.cin, (cuuint64_t)g.cout};
+      cuuint64_t str[1] = {(cuuint64_t)9 * g.cin * 4};
+      cuuint32_t box[2] = {32, (cuuint32_t)nt};
+      if ((rc = make_map_f32(&mB, w, 2, dims, str, box))) return rc;
+    } else {
+      cuuint64_t dims[3] = {32, (cuuint64_t)g.cout, (cuuint64_t)(9 * g.cin / 32)};
+      cuuint64_t str[2] = {(cuuint64_t)9 * g.cin * 4, 128};
+      cuuint32_t box[3] = {32, 32, (cuuint32_t)(nt / 32)};
+      if ((rc = make_map_f32(&mB, w, 3, dims, str, box))) return rc;
+    }
+    grid = dim3(m_tiles, n_tiles, p.splits);
+    if (out_m_tiles) *out_m_tiles = m_tiles;
+    if (mode == kFprop) return launch_conv_gemm_mode<kFprop>(nt, mA, mB, p, grid, stream);
+    return launch_conv_gemm_mode<kDgrad>(nt, mA, mB, p, grid, stream);
+  }
+  // wgrad
+  nt = nt_override > 0 ? nt_override : (g.cin >= 128 ? 128 : 64);
+  if (g.cin % nt) return set_error(-13, "N tile %d does not divide Cin %d", nt, g.cin);
+  int bw, bh, bn;
+  pixel_box(g.h, g.w, 32, &bw, &bh, &bn);
+  p.box_w = bw; p.box_h = bh; p.box_n = bn;
+  p.Ck = 0;
+  p.M_total = g.cout; p.N_total = g.cin;
+  p.k_iters = (int)((pixels + 31) / 32);
+  p.out_ld = (long long)9 * g.cin;
+  const int m_tiles = (g.cout + 127) / 128;
+  const int n_tiles = g.cin / nt;
+  p.splits = pick_splits(m_tiles * n_tiles * 9, p.k_iters, nt, splits_override);
+  {
+    cuuint64_t dims[3] = {32, (cuuint64_t)pixels, (cuuint64_t)(g.cout / 32)};
+    cuuint64_t str[2] = {(cuuint64_t)g.cout * 4, 128};
+    cuuint32_t box[3] = {32, 32, 4};
+    if ((rc = make_map_f32(&mA, in, 3, dims, str, box))) return rc;
+  }
+  {
+    cuuint64_t dims[5] = {32, (cuuint64_t)g.w, (cuuint64_t)g.h, (cuuint64_t)g.n, (cuuint64_t)(g.cin / 32)};
+    cuuint64_t str[4] = {(cuuint64_t)g.cin * 4, (cuuint64_t)g.w * g.cin * 4, (cuuint64_t)g.h * g.w * g.cin * 4, 128};
+    cuuint32_t box[5] = {32, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn, (cuuint32_t)(nt / 32)};
+    if ((rc = make_map_f32(&mB, in2, 5, dims, str, box))) return rc;
+  }
+  grid = dim3(m_tiles, n_tiles, 9 * p.splits);
+  if (out_m_tiles) *out_m_tiles = m_tiles;
+  return launch_conv_gemm_mode<kWgrad>(nt, mA, mB, p, grid, stream);
+}
+
+}  // namespace dpb

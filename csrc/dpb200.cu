@@ -1,0 +1,507 @@
+// libdpb200.so: C ABI over the sm_100a kernels (see include/dpb200.h).  Single translation unit.
+#include <cstring>
+#include <vector>
+#include <new>
+#include <cuda_runtime.h>
+
+#include "../include/dpb200.h"
+#include "errors.cuh"
+#include "ptx.cuh"
+#include "conv_gemm.cuh"
+#include "conv_gemm_host.cuh"
+#include "bn_relu_pool.cuh"
+#include "first_conv.cuh"
+#include "head_sgd.cuh"
+#include "comm.cuh"
+
+using namespace dpb;
+
+namespace {
+inline cudaStream_t S(dpb_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+constexpr int kBnBwdBlocks = 296;
+constexpr int kFirstWgradBlocks = 296;
+inline int grid_for(long long units, int threads, int cap) {
+  long long b = (units + threads - 1) / threads;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+}  // namespace
+
+extern "C" {
+
+int dpb_version(void) { return 100; }
+const char* dpb_last_error(void) { return error_buffer(); }
+
+int dpb_last_device_error(int* out5) {
+  DevError e;
+  DPB_CUDA(cudaMemcpyFromSymbol(&e, g_dpb_dev_error, sizeof(e)));
+  out5[0] = e.code; out5[1] = e.where; out5[2] = e.block; out5[3] = e.aux0; out5[4] = e.aux1;
+  DevError z{};
+  DPB_CUDA(cudaMemcpyToSymbol(g_dpb_dev_error, &z, sizeof(z)));
+  return 0;
+}
+
+size_t dpb_conv_workspace_bytes(void) { return kConvWorkspaceBytes; }
+size_t dpb_conv_counter_bytes(void) { return (size_t)kConvCounterSlots * sizeof(unsigned int); }
+
+// ------------------------------------------------------------------------------------------------ convolution
+int dpb_conv3x3_gemm(int mode, int n, int h, int w, int cin, int cout, const float* in, const float* in2,
+                     const float* weight, float* out, const float* bias, float* stat_sum, float* stat_sq,
+                     void* workspace, void* counters, int nt, int splits, int* m_tiles_out, dpb_stream_t stream) {
+  if (mode < 0 || mode > 2) return set_error(-1, "dpb_conv3x3_gemm: bad mode %d", mode);
+  ConvGeom g{n, h, w, cin, cout};
+  return conv_gemm_dispatch(mode, g, in, in2, weight, out, bias, stat_sum, stat_sq, (float*)workspace,
+                            (unsigned int*)counters, nt, splits, m_tiles_out, S(stream));
+}
+
+int dpb_first_conv_blocks(int n, int h, int w) {
+  const long long pix = (long long)n * h * w;
+  return (int)((pix + kFirstConvPixPerBlock - 1) / kFirstConvPixPerBlock);
+}
+
+int dpb_first_conv_fprop(const float* x, const float* weight, const float* bias, float* y, float* part_sum,
+                         float* part_sq, int n, int h, int w, dpb_stream_t stream) {
+  const int blocks = dpb_first_conv_blocks(n, h, w);
+  first_conv_fprop_kernel<<<blocks, 256, 0, S(stream)>>>(x, weight, bias, y, part_sum, part_sq, n, h, w);
+  DPB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int dpb_first_conv_wgrad_blocks(void) { return kFirstWgradBlocks; }
+
+int dpb_first_conv_wgrad(const float* x, const float* dy, float* partials, float* dw, int n, int h, int w,
+                         dpb_stream_t stream) {
+  const long long pix = (long long)n * h * w;
+  int blocks = (int)((pix + 63) / 64);
+  if (blocks > kFirstWgradBlocks) blocks = kFirstWgradBlocks;
+  first_conv_wgrad_kernel<<<blocks, 256, 0, S(stream)>>>(x, dy, partials, n, h, w);
+  DPB_CUDA(cudaGetLastError());
+  const int nout = 64 * 27;
+  column_reduce_kernel<<<(nout + 31) / 32, dim3(32, 8), 0, S(stream)>>>(partials, blocks, nout, dw);
+  DPB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ BN + ReLU + pool
+int dpb_bn_finalize(const float* part_sum, const float* part_sq, int parts, int c, double count, const float* gamma,
+                    const float* beta, float* running_mean, float* running_var, long long* nbt, float momentum,
+                    float eps, float* scale, float* shift, float* save_mean, float* save_invstd,
+                    dpb_stream_t stream) {
+  bn_finalize_kernel<<<(c + 31) / 32, dim3(32, 8), 0, S(stream)>>>(part_sum, part_sq, parts, c, count, gamma, beta,
+                                                                   running_mean, running_var, nbt, momentum, eps,
+                                                                   scale, shift, save_mean, save_invstd);
+  DPB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int dpb_bn_eval_scale_shift(int c, const float* gamma, const float* beta, const float* running_mean,
+                            const float* running_var, float eps, float* scale, float* shift, dpb_stream_t stream) {
+  bn_eval_scale_shift_kernel<<<(c + 127) / 128, 128, 0, S(stream)>>>(c, gamma, beta, running_mean, running_var, eps,
+                                                                    scale, shift);
+  DPB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int dpb_bn_relu_pool_fwd(const float* y, const float* scale, const float* shift, float* out, int n, int h, int w,
+                         int c, int pool, dpb_stream_t stream) {
+  if (c % 4) return set_error(-2, "bn_relu_pool: C must be a multiple of 4 (got %d)", c);
+  if (pool && ((h | w) & 1)) return set_error(-2, "bn_relu_pool: pooling needs even H, W (got %dx%d)", h, w);
+  const long long opix = pool ? (long long)n * (h / 2) * (w / 2) : (long long)n * h * w;
+  const long long units = opix * (c / 4);
+  const int blocks = grid_for(units, 256, 148 * 16);
+  if (pool)
+    bn_relu_pool_fwd_kernel<true><<<blocks, 256, 0, S(stream)>>>(y, scale, shift, out, units, c / 4, h, w);
+  else
+    bn_relu_pool_fwd_kernel<false><<<blocks, 256, 0, S(stream)>>>(y, scale, shift, out, units, c / 4, h, w);
+  DPB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int dpb_bn_bwd_blocks(void) { return kBnBwdBlocks; }
+
+int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, const float* shift,
+                         const float* save_mean, const float* save_invstd, const float* gamma, float* part,
+                         float* coef, float* dgamma, float* dbeta, float* conv_dbias, float* dy, int n, int h, int w,
+                         int c, int pool, dpb_stream_t stream) {
+  if (c % 4 || c > 1024) return set_error(-2, "bn_relu_pool_bwd: C must be a multiple of 4 and <= 1024 (got %d)", c);
+  const int c4 = c / 4;
+  const long long opix = pool ? (long long)n * (h / 2) * (w / 2) : (long long)n * h * w;
+  const int pl = 256 / c4;
+  int blocks = (int)((opix + pl - 1) / pl);
+  if (blocks > kBnBwdBlocks) blocks = kBnBwdBlocks;
+  float* part_g = part;
+  float* part_gx = part + (size_t)kBnBwdBlocks * c;
+  const size_t smem = 2 * 256 * sizeof(float4);
+  if (pool)
+    bn_bwd_reduce_kernel<true><<<blocks, 256, smem, S(stream)>>>(y, dout, scale, shift, save_mean, save_invstd,
+                                                                 part_g, part_gx, opix, c4, h, w);
+  else
+    bn_bwd_reduce_kernel<false><<<blocks, 256, smem, S(stream)>>>(y, dout, scale, shift, save_mean, save_invstd,
+                                                                  part_g, part_gx, opix, c4, h, w);
+  DPB_CUDA(cudaGetLastError());
+  const double count = (double)n * h * w;
+  bn_bwd_finalize_kernel<<<(c + 31) / 32, dim3(32, 8), 0, S(stream)>>>(part_g, part_gx, blocks, c, count, gamma,
+                                                                       save_mean, save_invstd, dgamma, dbeta, conv_dbias,
+                                                                       coef);
+  DPB_CUDA(cudaGetLastError());
+  const long long units = opix * c4;
+  const int ablocks = grid_for(units, 256, 148 * 16);
+  if (pool)
+    bn_bwd_apply_kernel<true><<<ablocks, 256, 0, S(stream)>>>(y, dout, scale, shift, coef, dy, units, c, h, w);
+  else
+    bn_bwd_apply_kernel<false><<<ablocks, 256, 0, S(stream)>>>(y, dout, scale, shift, coef, dy, units, c, h, w);
+  DPB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ head / loss
+int dpb_linear_fwd(const float* x, const float* w, const float* bias, float* out, int b, int k, int o,
+                   dpb_stream_t stream) {
+  if (o > kMaxClasses) return set_error(-3, "linear: out_features %d > %d", o, kMaxClasses);
+  linear_fwd_kernel<<<(b * 32 + 255) / 256, 256, 0, S(stream)>>>(x, w, bias, out, b, k, o);
+  DPB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int dpb_linear_bwd(const float* dz, const float* x, const float* w, float* dx, float* dw, float* db, int b, int k,
+                   int o, dpb_stream_t stream) {
+  if (o > kMaxClasses) return set_error(-3, "linear: out_features %d > %d", o, kMaxClasses);
+  if (dx != nullptr) {
+    const long long n = (long long)b * k;
+    linear_bwd_input_kernel<<<(int)((n + 255) / 256), 256, 0, S(stream)>>>(dz, w, dx, b, k, o);
+    DPB_CUDA(cudaGetLastError());
+  }
+  if (dw != nullptr) {
+    linear_bwd_weight_kernel<<<(k + 31) / 32, dim3(32, 8), 0, S(stream)>>>(dz, x, dw, db, b, k, o);
+    DPB_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+int dpb_cross_entropy_fwd(const float* logits, const long long* target, float* loss, float* metrics, int b, int o,
+                          dpb_stream_t stream) {
+  cross_entropy_fwd_kernel<<<1, 256, 0, S(stream)>>>(logits, target, loss, metrics, b, o);
+  DPB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int dpb_cross_entropy_bwd(const float* logits, const long long* target, const float* grad_out, float* dz, int b,
+                          int o, dpb_stream_t stream) {
+  cross_entropy_bwd_kernel<<<(b + 255) / 256, 256, 0, S(stream)>>>(logits, target, grad_out, dz, b, o);
+  DPB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ optimizer
+int dpb_sgd_step(float* p, const float* g, float* m, long long n, float lr, float momentum, float wd,
+                 float grad_scale, int nesterov, dpb_stream_t stream) {
+  if (n <= 0) return 0;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) |
+                         reinterpret_cast<uintptr_t>(m)) & 15) == 0;
+  long long n4 = aligned ? n / 4 : 0;
+  if (n4 > 0) {
+    sgd_kernel<<<grid_for(n4, 256, 148 * 8), 256, 0, S(stream)>>>(p, g, m, n4, lr, momentum, wd, grad_scale,
+                                                                  nesterov);
+    DPB_CUDA(cudaGetLastError());
+  }
+  const long long rem = n - n4 * 4;
+  if (rem > 0) {
+    const long long o = n4 * 4;
+    sgd_scalar_kernel<<<(int)((rem + 255) / 256), 256, 0, S(stream)>>>(p + o, g + o, m ? m + o : nullptr, rem, lr,
+                                                                       momentum, wd, grad_scale, nesterov);
+    DPB_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ symmetric memory
+int dpb_symm_alloc(size_t bytes, void** ptr) {
+  DPB_CUDA(cudaMalloc(ptr, bytes));
+  DPB_CUDA(cudaMemset(*ptr, 0, bytes));
+  DPB_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+int dpb_symm_free(void* ptr) {
+  DPB_CUDA(cudaFree(ptr));
+  return 0;
+}
+int dpb_symm_export(void* ptr, unsigned char handle64[64]) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  cudaIpcMemHandle_t h;
+  DPB_CUDA(cudaIpcGetMemHandle(&h, ptr));
+  memcpy(handle64, &h, 64);
+  return 0;
+}
+int dpb_symm_import(const unsigned char handle64[64], void** peer_ptr) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  DPB_CUDA(cudaIpcOpenMemHandle(peer_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+int dpb_symm_close(void* peer_ptr) {
+  DPB_CUDA(cudaIpcCloseMemHandle(peer_ptr));
+  return 0;
+}
+size_t dpb_signal_pad_bytes(void) { return kSigPadBytes; }
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------ communicator
+struct dpb_comm {
+  CommCtx ctx;
+  int emulate;
+};
+
+namespace {
+
+PeerPtrs make_ptrs(void* const* bufs, int n) {
+  PeerPtrs p{};
+  for (int i = 0; i < n && i < kMaxRanks; ++i) p.p[i] = bufs ? reinterpret_cast<float*>(bufs[i]) : nullptr;
+  return p;
+}
+
+template <typename K, typename... Args>
+int launch_comm(dpb_comm* c, K kern_real, K kern_emu, int blocks, int threads, cudaStream_t st, Args... args) {
+  if (blocks < 1) blocks = 1;
+  if (blocks > kCommMaxBlocks) blocks = kCommMaxBlocks;
+  if (!c->emulate) {
+    kern_real<<<blocks, threads, 0, st>>>(args...);
+    DPB_CUDA(cudaGetLastError());
+    return 0;
+  }
+  void* params[] = {(void*)&args...};
+  dim3 grid(blocks, c->ctx.nranks);
+  DPB_CUDA(cudaLaunchCooperativeKernel((const void*)kern_emu, grid, dim3(threads), params, 0, st));
+  return 0;
+}
+
+int comm_blocks_for(long long n4, int threads, int u, int want) {
+  if (want > 0) return want > kCommMaxBlocks ? kCommMaxBlocks : want;
+  long long b = (n4 + (long long)threads * u - 1) / ((long long)threads * u);
+  if (b > 64) b = 64;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+int check_range(const char* what, long long offset, long long count) {
+  if ((offset & 3) || (count & 3) || count < 0)
+    return set_error(-4, "%s: offset/count must be multiples of 4 floats (got %lld, %lld)", what, offset, count);
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int dpb_comm_create(int rank, int nranks, void* const* signal_pads, int emulate, dpb_comm** out) {
+  if (nranks < 1 || nranks > kMaxRanks) return set_error(-5, "comm: world size %d outside [1,%d]", nranks, kMaxRanks);
+  if (rank < 0 || rank >= nranks) return set_error(-5, "comm: bad rank %d", rank);
+  dpb_comm* c = new (std::nothrow) dpb_comm();
+  if (!c) return set_error(-5, "comm: out of host memory");
+  c->ctx.rank = rank;
+  c->ctx.nranks = nranks;
+  for (int i = 0; i < kMaxRanks; ++i) c->ctx.sig[i] = i < nranks ? reinterpret_cast<uint32_t*>(signal_pads[i]) : nullptr;
+  c->emulate = emulate;
+  *out = c;
+  return 0;
+}
+int dpb_comm_destroy(dpb_comm* c) {
+  delete c;
+  return 0;
+}
+
+int dpb_allreduce_sgd(dpb_comm* c, int channel, void* const* grads, void* const* params, void* const* momentum,
+                      long long offset, long long count, float scale, float lr, float mom, float wd, int nesterov,
+                      int write_mean, int blocks, dpb_stream_t stream) {
+  int rc = check_range("allreduce", offset, count);
+  if (rc) return rc;
+  if (count == 0) return 0;
+  const int nr = c->ctx.nranks;
+  const long long n4 = count / 4, off4 = offset / 4;
+  SgdArgs sg{};
+  sg.enabled = params != nullptr;
+  sg.lr = lr; sg.momentum = mom; sg.wd = wd; sg.nesterov = nesterov;
+  PeerPtrs d = make_ptrs(grads, nr), pp = make_ptrs(params, nr), mm = make_ptrs(momentum, nr);
+  const long long slice = (n4 + nr - 1) / nr;
+  cudaStream_t st = S(stream);
+#define DPB_TWOSHOT(NRT, U)                                                                                      \
+  return launch_comm(c, allreduce_twoshot_kernel<false, NRT, U>, allreduce_twoshot_kernel<true, NRT, U>,         \
+                     comm_blocks_for(slice, 512, U, blocks), 512, st, c->ctx, channel, d, off4, n4, scale,        \
+                     write_mean, sg, pp, mm)
+  switch (nr) {
+    case 1: DPB_TWOSHOT(1, 4);
+    case 2: DPB_TWOSHOT(2, 4);
+    case 4: DPB_TWOSHOT(4, 4);
+    case 8: DPB_TWOSHOT(8, 2);
+    default: DPB_TWOSHOT(0, 2);
+  }
+#undef DPB_TWOSHOT
+}
+
+int dpb_allreduce(dpb_comm* c, int channel, void* const* bufs, long long offset, long long count, float scale,
+                  int algo, int blocks, dpb_stream_t stream) {
+  int rc = check_range("allreduce", offset, count);
+  if (rc) return rc;
+  if (count == 0) return 0;
+  const long long n4 = count / 4;
+  constexpr int U = 4;
+  if (algo == 0) algo = (n4 * 16 <= (256 << 10)) ? 1 : 2;  // <= 256 KiB: one-shot
+  if (algo == 1) {
+    int b = (int)((n4 + 512LL * U - 1) / (512LL * U));
+    if (b <= kCommMaxBlocks) {
+      PeerPtrs d = make_ptrs(bufs, c->ctx.nranks);
+      return launch_comm(c, allreduce_oneshot_kernel<false, U>, allreduce_oneshot_kernel<true, U>, b, 512, S(stream),
+                         c->ctx, channel, d, offset / 4, n4, scale);
+    }
+  }
+  return dpb_allreduce_sgd(c, channel, bufs, nullptr, nullptr, offset, count, scale, 0.f, 0.f, 0.f, 0, 1, blocks,
+                           stream);
+}
+
+int dpb_gather_mean_scatter(dpb_comm* c, int channel, void* const* bufs, long long offset, long long count,
+                            float scale, int root, int blocks, dpb_stream_t stream) {
+  int rc = check_range("gather_mean_scatter", offset, count);
+  if (rc) return rc;
+  if (count == 0) return 0;
+  const long long n4 = count / 4;
+  constexpr int U = 2;
+  PeerPtrs d = make_ptrs(bufs, c->ctx.nranks);
+  int b = comm_blocks_for(n4, 512, U, blocks);
+  if (blocks <= 0 && n4 > 64LL * 512 * U) b = kCommMaxBlocks;  // the root needs every SM it can get
+  return launch_comm(c, gather_mean_scatter_kernel<false, U>, gather_mean_scatter_kernel<true, U>, b, 512, S(stream),
+                     c->ctx, channel, d, offset / 4, n4, scale, root);
+}
+
+int dpb_broadcast(dpb_comm* c, int channel, void* const* bufs, long long offset16, long long count16, int root,
+                  int blocks, dpb_stream_t stream) {
+  if (count16 <= 0) return 0;
+  PeerPtrs d = make_ptrs(bufs, c->ctx.nranks);
+  return launch_comm(c, broadcast_kernel<false>, broadcast_kernel<true>, comm_blocks_for(count16, 512, 4, blocks), 512,
+                     S(stream), c->ctx, channel, d, offset16, count16, root);
+}
+
+int dpb_barrier(dpb_comm* c, int channel, dpb_stream_t stream) {
+  return launch_comm(c, barrier_kernel<false>, barrier_kernel<true>, 1, 32, S(stream), c->ctx, channel);
+}
+
+// ------------------------------------------------------------------------------------------------ DDP reducer
+int dpb_plan_buckets(int nparams, const long long* bytes, long long first_cap, long long cap, int* bucket_of_param) {
+  int bucket = 0;
+  long long fill = 0;
+  long long limit = first_cap;
+  for (int i = 0; i < nparams; ++i) {
+    bucket_of_param[i] = bucket;
+    fill += bytes[i];
+    if (fill >= limit && i + 1 < nparams) {  // the overflowing tensor stays; the bucket closes behind it
+      ++bucket;
+      fill = 0;
+      limit = cap;
+    }
+  }
+  return nparams > 0 ? bucket + 1 : 0;
+}
+
+}  // extern "C"
+
+struct dpb_reducer {
+  dpb_comm* comm;
+  int nparams, nbuckets;
+  std::vector<int> bucket_of_param;
+  std::vector<long long> b_lo, b_hi;  // float offsets of each bucket's arena range
+  std::vector<int> b_total, b_pending;
+  std::vector<void*> bufs;
+  float scale;
+  cudaStream_t side;
+  cudaEvent_t ev_ready, ev_done;
+  int launched;
+};
+
+extern "C" {
+
+int dpb_reducer_create(dpb_comm* c, int nparams, const long long* offsets, const long long* counts,
+                       const int* bucket_of_param, int nbuckets, void* const* grad_bufs, float scale,
+                       dpb_reducer** out) {
+  dpb_reducer* r = new (std::nothrow) dpb_reducer();
+  if (!r) return set_error(-6, "reducer: out of host memory");
+  r->comm = c;
+  r->nparams = nparams;
+  r->nbuckets = nbuckets;
+  r->bucket_of_param.assign(bucket_of_param, bucket_of_param + nparams);
+  r->b_lo.assign(nbuckets, -1);
+  r->b_hi.assign(nbuckets, -1);
+  r->b_total.assign(nbuckets, 0);
+  r->b_pending.assign(nbuckets, 0);
+  for (int i = 0; i < nparams; ++i) {
+    const int b = bucket_of_param[i];
+    if (b < 0 || b >= nbuckets) { delete r; return set_error(-6, "reducer: bad bucket id %d", b); }
+    if ((offsets[i] & 3) || (counts[i] & 3)) { delete r; return set_error(-6, "reducer: param %d not 16-byte granular", i); }
+    if (r->b_lo[b] < 0 || offsets[i] < r->b_lo[b]) r->b_lo[b] = offsets[i];
+    if (offsets[i] + counts[i] > r->b_hi[b]) r->b_hi[b] = offsets[i] + counts[i];
+    r->b_total[b]++;
+  }
+  // contiguity: bucket ranges must not overlap
+  for (int a = 0; a < nbuckets; ++a)
+    for (int b = a + 1; b < nbuckets; ++b)
+      if (r->b_lo[a] < r->b_hi[b] && r->b_lo[b] < r->b_hi[a]) {
+        delete r;
+        return set_error(-6, "reducer: buckets %d and %d overlap in the arena", a, b);
+      }
+  r->bufs.assign(grad_bufs, grad_bufs + c->ctx.nranks);
+  r->scale = scale;
+  r->launched = 0;
+  if (cudaStreamCreateWithFlags(&r->side, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&r->ev_ready, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&r->ev_done, cudaEventDisableTiming) != cudaSuccess) {
+    delete r;
+    return set_error(-6, "reducer: stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));
+  }
+  *out = r;
+  return 0;
+}
+
+int dpb_reducer_destroy(dpb_reducer* r) {
+  if (!r) return 0;
+  cudaStreamDestroy(r->side);
+  cudaEventDestroy(r->ev_ready);
+  cudaEventDestroy(r->ev_done);
+  delete r;
+  return 0;
+}
+
+int dpb_reducer_prepare(dpb_reducer* r) {
+  r->b_pending = r->b_total;
+  r->launched = 0;
+  return 0;
+}
+
+int dpb_reducer_mark_ready(dpb_reducer* r, int param, dpb_stream_t main_stream) {
+  if (param < 0 || param >= r->nparams) return set_error(-6, "reducer: bad param index %d", param);
+  const int b = r->bucket_of_param[param];
+  if (r->b_pending[b] <= 0) return set_error(-6, "reducer: param %d marked ready twice (bucket %d)", param, b);
+  if (--r->b_pending[b] > 0) return 0;
+  // bucket complete: side stream picks up after everything enqueued on the main stream so far
+  DPB_CUDA(cudaEventRecord(r->ev_ready, S(main_stream)));
+  DPB_CUDA(cudaStreamWaitEvent(r->side, r->ev_ready, 0));
+  int rc = dpb_allreduce(r->comm, /*channel=*/1, r->bufs.data(), r->b_lo[b], r->b_hi[b] - r->b_lo[b], r->scale,
+                         /*algo=*/0, /*blocks=*/0, r->side);
+  if (rc) return rc;
+  r->launched++;
+  return 0;
+}
+
+int dpb_reducer_finalize(dpb_reducer* r, dpb_stream_t main_stream) {
+  for (int b = 0; b < r->nbuckets; ++b)
+    if (r->b_pending[b] != 0 && r->b_pending[b] != r->b_total[b])
+      return set_error(-6, "reducer: bucket %d incomplete at finalize (%d of %d pending)", b, r->b_pending[b],
+                       r->b_total[b]);
+  if (r->launched > 0) {
+    DPB_CUDA(cudaEventRecord(r->ev_done, r->side));
+    DPB_CUDA(cudaStreamWaitEvent(S(main_stream), r->ev_done, 0));
+  }
+  return 0;
+}
+
+int dpb_reducer_launched(dpb_reducer* r) { return r->launched; }
+
+}  // extern "C"

@@ -1,0 +1,191 @@
+"""Differentiable ops of the framework.
+
+On CUDA tensors every op is a ``torch.autograd.Function`` over the sm_100a kernels in ``libdpb200.so`` (no cuDNN, no
+cuBLAS, no Triton).  On CPU tensors the same functions evaluate the plain PyTorch fp32 formulas: that path is the
+numerical oracle of the tests and what ``main.py`` runs for the reference's CPU configuration; it is never taken for a
+CUDA tensor.
+
+The unit of fusion is the reference's repeating block ``Conv2d(3x3) -> BatchNorm2d -> ReLU [-> MaxPool2d(2,2)]``
+(reference model.py:14-26).
+
+Gradient placement: when a parameter has been adopted by a :class:`~distributed_pytorch_b200.utils.arena.FlatArena`,
+its gradient is written straight into the flat (NVLink-symmetric) gradient arena and the returned tensor is a fresh
+view of that memory.  Autograd's ``AccumulateGrad`` adopts such a tensor without copying when ``param.grad`` is None
+(the reference calls ``optimizer.zero_grad()`` every iteration, main.py:32), so the "bucket" *is* the gradient memory.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+from . import kernels as K
+
+__all__ = ["conv_bn_relu_pool", "linear", "cross_entropy", "grad_destination"]
+
+
+def grad_destination(param: torch.Tensor) -> torch.Tensor:
+    """Where the gradient of ``param`` should be written by a backward kernel."""
+    slot = getattr(param, "_dpb_grad_slot", None)
+    if slot is not None:
+        g = param.grad
+        view = slot()
+        if g is None or g.data_ptr() != view.data_ptr():
+            return view
+        # param.grad already lives in the arena (gradient accumulation): autograd will add, so use a temporary
+    return torch.empty_strided(param.shape, param.stride(), device=param.device, dtype=param.dtype)
+
+
+def _as_nhwc(t: torch.Tensor) -> torch.Tensor:
+    return t if K.is_nhwc(t) else t.contiguous(memory_format=torch.channels_last)
+
+
+def _as_krsc(w: torch.Tensor) -> torch.Tensor:
+    return w if K.is_nhwc(w) else w.contiguous(memory_format=torch.channels_last)
+
+
+class _ConvBnReluPool(torch.autograd.Function):
+    """Fused block, CUDA.  Saves only X, the raw conv output Y and four per-channel vectors."""
+
+    @staticmethod
+    def forward(ctx, x, conv_w, conv_b, bn_w, bn_b, running_mean, running_var, nbt, training, momentum, eps, pool):
+        n, cin, h, w = x.shape
+        cout = conv_w.shape[0]
+        first = cin == 3
+        wk = _as_krsc(conv_w.detach())
+        if first:
+            if cout != 64:
+                raise NotImplementedError("the Cin=3 entry layer kernel is built for 64 output channels")
+            xin = x.detach().contiguous()  # NCHW as delivered by the loader
+        else:
+            xin = _as_nhwc(x.detach())
+        y = K.nhwc_empty(n, cout, h, w, x.device)
+        if training:
+            if first:
+                ps, pq, parts = K.first_conv_fprop(xin, wk, conv_b, y, True)
+            else:
+                ps, pq, parts = K.conv3x3_gemm(0, n, h, w, cin, cout, xin, None, wk, y, conv_b, want_stats=True)
+            stats = K.bn_finalize(ps, pq, parts, cout, float(n * h * w), bn_w, bn_b, running_mean, running_var, nbt,
+                                  momentum, eps)
+        else:
+            if first:
+                K.first_conv_fprop(xin, wk, conv_b, y, False)
+            else:
+                K.conv3x3_gemm(0, n, h, w, cin, cout, xin, None, wk, y, conv_b, want_stats=False)
+            stats = K.bn_eval_scale_shift(cout, bn_w, bn_b, running_mean, running_var, eps)
+        out = K.bn_relu_pool_fwd(y, stats[0], stats[1], pool)
+        ctx.pool = pool
+        ctx.first = first
+        ctx.training = training
+        ctx.params = (conv_w, conv_b, bn_w, bn_b)
+        ctx.save_for_backward(xin, wk, y, stats)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        xin, wk, y, stats = ctx.saved_tensors
+        conv_w, conv_b, bn_w, bn_b = ctx.params
+        if not ctx.training:
+            raise RuntimeError("backward through an eval-mode BatchNorm block is not supported")
+        n, cout, h, w = y.shape
+        cin = conv_w.shape[1]
+        dout = _as_nhwc(dout) if dout.dim() == 4 else dout.contiguous()
+        d_bn_w = grad_destination(bn_w)
+        d_bn_b = grad_destination(bn_b)
+        d_conv_b = grad_destination(conv_b) if conv_b is not None else None
+        dy = K.bn_relu_pool_bwd(y, dout, stats, bn_w, d_bn_w, d_bn_b, d_conv_b, ctx.pool)
+        d_conv_w = grad_destination(conv_w)
+        if not K.is_nhwc(d_conv_w):
+            raise RuntimeError("conv weight gradients must be KRSC (channels_last) in memory")
+        dx = None
+        if ctx.first:
+            K.first_conv_wgrad(xin, dy, d_conv_w)
+        else:
+            K.conv3x3_gemm(2, n, h, w, cin, cout, dy, xin, wk, d_conv_w)
+            if ctx.needs_input_grad[0]:
+                dx = K.nhwc_empty(n, cin, h, w, y.device)
+                K.conv3x3_gemm(1, n, h, w, cin, cout, dy, None, wk, dx)
+        return dx, d_conv_w, d_conv_b, d_bn_w, d_bn_b, None, None, None, None, None, None, None
+
+
+def conv_bn_relu_pool(x, conv_w, conv_b, bn_w, bn_b, running_mean, running_var, num_batches_tracked,
+                      training: bool, momentum: float = 0.1, eps: float = 1e-5, pool: bool = False):
+    """Conv3x3(s1,p1,bias) -> BatchNorm2d -> ReLU [-> MaxPool2d(2,2)].  (reference model.py:16-25)"""
+    if x.is_cuda:
+        return _ConvBnReluPool.apply(x, conv_w, conv_b, bn_w, bn_b, running_mean, running_var, num_batches_tracked,
+                                     training, momentum, eps, pool)
+    # CPU oracle
+    y = F.conv2d(x, conv_w, conv_b, stride=1, padding=1)
+    if training and num_batches_tracked is not None:
+        num_batches_tracked += 1
+    y = F.batch_norm(y, running_mean, running_var, bn_w, bn_b, training, momentum, eps)
+    y = F.relu(y)
+    if pool:
+        y = F.max_pool2d(y, 2, 2)
+    return y
+
+
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b):
+        xc = x.detach().contiguous()
+        wc = w.detach().contiguous()
+        out = K.linear_fwd(xc, wc, b)
+        ctx.params = (w, b)
+        ctx.save_for_backward(xc, wc)
+        return out
+
+    @staticmethod
+    def backward(ctx, dz):
+        xc, wc = ctx.saved_tensors
+        w, b = ctx.params
+        dz = dz.contiguous()
+        dx = torch.empty_like(xc) if ctx.needs_input_grad[0] else None
+        dw = grad_destination(w)
+        db = grad_destination(b) if b is not None else None
+        K.linear_bwd(dz, xc, wc, dx, dw, db)
+        return dx, dw, db
+
+
+def linear(x, w, b):
+    """y = x W^T + b  (reference model.py:40,45)."""
+    if x.is_cuda:
+        return _Linear.apply(x, w, b)
+    return F.linear(x, w, b)
+
+
+class _CrossEntropy(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target):
+        lg = logits.detach().contiguous()
+        tg = target.contiguous()
+        loss = K.cross_entropy_fwd(lg, tg)
+        ctx.save_for_backward(lg, tg)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        lg, tg = ctx.saved_tensors
+        return K.cross_entropy_bwd(lg, tg, gout.contiguous()), None
+
+
+def cross_entropy(logits, target):
+    """Mean-reduced softmax cross-entropy (reference main.py:34,99 ``CrossEntropyLoss()``)."""
+    if logits.is_cuda:
+        if target.dtype != torch.int64:
+            target = target.long()
+        return _CrossEntropy.apply(logits, target)
+    return F.cross_entropy(logits, target)
+
+
+def eval_metrics(logits, target, metrics: Optional[torch.Tensor]):
+    """Adds the batch-mean loss to ``metrics[0]`` and the number of arg-max hits to ``metrics[1]`` on the device
+    (reference main.py:59-61 does this with two ``.item()`` syncs per batch)."""
+    if logits.is_cuda:
+        return K.cross_entropy_fwd(logits.detach().contiguous(), target.long().contiguous(), metrics)
+    loss = F.cross_entropy(logits, target)
+    if metrics is not None:
+        metrics[0] += loss
+        metrics[1] += (logits.argmax(1) == target).sum()
+    return loss

@@ -1,0 +1,199 @@
+"""Thin Python launchers over the C ABI of ``libdpb200.so`` (one function per kernel group).
+
+All tensors are fp32 CUDA tensors; activations are NHWC in memory (PyTorch ``channels_last`` tensors of logical shape
+``(N, C, H, W)``), conv weights are KRSC in memory (``channels_last`` views of ``(Cout, Cin, 3, 3)``).  Every launcher
+enqueues on ``torch.cuda.current_stream()`` and returns immediately.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+
+from .. import _native as N
+
+__all__ = [
+    "Scratch", "scratch", "conv3x3_gemm", "first_conv_fprop", "first_conv_wgrad", "bn_finalize", "bn_eval_scale_shift",
+    "bn_relu_pool_fwd", "bn_relu_pool_bwd", "linear_fwd", "linear_bwd", "cross_entropy_fwd", "cross_entropy_bwd",
+    "sgd_step", "is_nhwc", "nhwc_empty",
+]
+
+
+def is_nhwc(t: torch.Tensor) -> bool:
+    """True if a 4-D tensor is dense NHWC in memory."""
+    if t.dim() != 4:
+        return False
+    n, c, h, w = t.shape
+    return t.stride() == (h * w * c, 1, w * c, c) or t.is_contiguous(memory_format=torch.channels_last)
+
+
+def nhwc_empty(n: int, c: int, h: int, w: int, device) -> torch.Tensor:
+    return torch.empty((n, c, h, w), device=device, dtype=torch.float32, memory_format=torch.channels_last)
+
+
+class Scratch:
+    """Per-device scratch the kernels share (stream-ordered reuse): split-K partial tiles and arrival counters for
+    the tensor-core conv, BatchNorm-backward partial sums and coefficients, first-layer wgrad partials."""
+
+    def __init__(self, device: torch.device):
+        lib = N.require()
+        self.device = device
+        self.conv_ws = torch.empty(lib.dpb_conv_workspace_bytes() // 4, device=device, dtype=torch.float32)
+        self.conv_counters = torch.zeros(lib.dpb_conv_counter_bytes() // 4, device=device, dtype=torch.int32)
+        self.bn_blocks = lib.dpb_bn_bwd_blocks()
+        self.bn_part = torch.empty(2 * self.bn_blocks * 1024, device=device, dtype=torch.float32)
+        self.bn_coef = torch.empty(3 * 1024, device=device, dtype=torch.float32)
+        self.fc_wgrad_part = torch.empty(lib.dpb_first_conv_wgrad_blocks() * 64 * 27, device=device, dtype=torch.float32)
+
+
+_scratch: dict[int, Scratch] = {}
+
+
+def scratch(device: torch.device) -> Scratch:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    s = _scratch.get(idx)
+    if s is None:
+        s = Scratch(torch.device("cuda", idx))
+        _scratch[idx] = s
+    return s
+
+
+def conv3x3_gemm(mode: int, n: int, h: int, w: int, cin: int, cout: int, inp: torch.Tensor,
+                 inp2: Optional[torch.Tensor], weight: torch.Tensor, out: torch.Tensor,
+                 bias: Optional[torch.Tensor] = None, want_stats: bool = False, nt: int = 0, splits: int = 0):
+    """tcgen05 implicit-GEMM conv. mode 0 fprop / 1 dgrad / 2 wgrad. Returns (stat_sum, stat_sq, m_tiles) for fprop
+    with ``want_stats`` else None."""
+    lib = N.require()
+    sc = scratch(out.device)
+    stat_sum = stat_sq = None
+    m_tiles = ctypes.c_int(0)
+    if want_stats:
+        tiles = (n * h * w + 127) // 128
+        stat_sum = torch.empty((tiles, cout), device=out.device, dtype=torch.float32)
+        stat_sq = torch.empty((tiles, cout), device=out.device, dtype=torch.float32)
+    N.check(lib.dpb_conv3x3_gemm(mode, n, h, w, cin, cout, N.ptr(inp), N.ptr(inp2), N.ptr(weight), N.ptr(out),
+                                 N.ptr(bias), N.ptr(stat_sum), N.ptr(stat_sq), N.ptr(sc.conv_ws),
+                                 N.ptr(sc.conv_counters), nt, splits, ctypes.byref(m_tiles), N.stream()),
+            "dpb_conv3x3_gemm")
+    N.count_launches(1)
+    if want_stats:
+        return stat_sum, stat_sq, m_tiles.value
+    return None
+
+
+def first_conv_fprop(x_nchw: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], y: torch.Tensor,
+                     want_stats: bool):
+    lib = N.require()
+    n, _, h, w = x_nchw.shape
+    blocks = lib.dpb_first_conv_blocks(n, h, w)
+    ps = pq = None
+    if want_stats:
+        ps = torch.empty((blocks, 64), device=y.device, dtype=torch.float32)
+        pq = torch.empty((blocks, 64), device=y.device, dtype=torch.float32)
+    N.check(lib.dpb_first_conv_fprop(N.ptr(x_nchw), N.ptr(weight), N.ptr(bias), N.ptr(y), N.ptr(ps), N.ptr(pq), n, h,
+                                     w, N.stream()), "dpb_first_conv_fprop")
+    N.count_launches(1)
+    return ps, pq, blocks
+
+
+def first_conv_wgrad(x_nchw: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor):
+    lib = N.require()
+    n, _, h, w = x_nchw.shape
+    sc = scratch(dy.device)
+    N.check(lib.dpb_first_conv_wgrad(N.ptr(x_nchw), N.ptr(dy), N.ptr(sc.fc_wgrad_part), N.ptr(dw), n, h, w,
+                                     N.stream()), "dpb_first_conv_wgrad")
+    N.count_launches(2)
+
+
+def bn_finalize(part_sum, part_sq, parts: int, c: int, count: float, gamma, beta, running_mean, running_var, nbt,
+                momentum: float, eps: float):
+    lib = N.require()
+    dev = part_sum.device
+    out = torch.empty((4, c), device=dev, dtype=torch.float32)  # scale, shift, mean, invstd
+    N.check(lib.dpb_bn_finalize(N.ptr(part_sum), N.ptr(part_sq), parts, c, float(count), N.ptr(gamma), N.ptr(beta),
+                                N.ptr(running_mean), N.ptr(running_var), N.ptr(nbt), momentum, eps, N.ptr(out[0]),
+                                N.ptr(out[1]), N.ptr(out[2]), N.ptr(out[3]), N.stream()), "dpb_bn_finalize")
+    N.count_launches(1)
+    return out
+
+
+def bn_eval_scale_shift(c: int, gamma, beta, running_mean, running_var, eps: float):
+    lib = N.require()
+    out = torch.empty((2, c), device=gamma.device, dtype=torch.float32)
+    N.check(lib.dpb_bn_eval_scale_shift(c, N.ptr(gamma), N.ptr(beta), N.ptr(running_mean), N.ptr(running_var), eps,
+                                        N.ptr(out[0]), N.ptr(out[1]), N.stream()), "dpb_bn_eval_scale_shift")
+    N.count_launches(1)
+    return out
+
+
+def bn_relu_pool_fwd(y: torch.Tensor, scale, shift, pool: bool) -> torch.Tensor:
+    lib = N.require()
+    n, c, h, w = y.shape
+    out = nhwc_empty(n, c, h // 2 if pool else h, w // 2 if pool else w, y.device)
+    N.check(lib.dpb_bn_relu_pool_fwd(N.ptr(y), N.ptr(scale), N.ptr(shift), N.ptr(out), n, h, w, c, int(pool),
+                                     N.stream()), "dpb_bn_relu_pool_fwd")
+    N.count_launches(1)
+    return out
+
+
+def bn_relu_pool_bwd(y, dout, stats, gamma, dgamma, dbeta, conv_dbias, pool: bool) -> torch.Tensor:
+    """stats = (4, C) tensor from bn_finalize. Writes dgamma/dbeta, returns dY (NHWC, conv resolution)."""
+    lib = N.require()
+    n, c, h, w = y.shape
+    sc = scratch(y.device)
+    dy = torch.empty_like(y)
+    N.check(lib.dpb_bn_relu_pool_bwd(N.ptr(y), N.ptr(dout), N.ptr(stats[0]), N.ptr(stats[1]), N.ptr(stats[2]),
+                                     N.ptr(stats[3]), N.ptr(gamma), N.ptr(sc.bn_part), N.ptr(sc.bn_coef),
+                                     N.ptr(dgamma), N.ptr(dbeta), N.ptr(conv_dbias), N.ptr(dy), n, h, w, c, int(pool),
+                                     N.stream()),
+            "dpb_bn_relu_pool_bwd")
+    N.count_launches(3)
+    return dy
+
+
+def linear_fwd(x, w, b) -> torch.Tensor:
+    lib = N.require()
+    bsz, k = x.shape
+    o = w.shape[0]
+    out = torch.empty((bsz, o), device=x.device, dtype=torch.float32)
+    N.check(lib.dpb_linear_fwd(N.ptr(x), N.ptr(w), N.ptr(b), N.ptr(out), bsz, k, o, N.stream()), "dpb_linear_fwd")
+    N.count_launches(1)
+    return out
+
+
+def linear_bwd(dz, x, w, dx, dw, db) -> None:
+    lib = N.require()
+    bsz, k = x.shape
+    o = w.shape[0]
+    N.check(lib.dpb_linear_bwd(N.ptr(dz), N.ptr(x), N.ptr(w), N.ptr(dx), N.ptr(dw), N.ptr(db), bsz, k, o, N.stream()),
+            "dpb_linear_bwd")
+    N.count_launches((1 if dx is not None else 0) + (1 if dw is not None else 0))
+
+
+def cross_entropy_fwd(logits, target, metrics=None) -> torch.Tensor:
+    lib = N.require()
+    bsz, o = logits.shape
+    loss = torch.empty((), device=logits.device, dtype=torch.float32)
+    N.check(lib.dpb_cross_entropy_fwd(N.ptr(logits), N.ptr(target), N.ptr(loss), N.ptr(metrics), bsz, o, N.stream()),
+            "dpb_cross_entropy_fwd")
+    N.count_launches(1)
+    return loss
+
+
+def cross_entropy_bwd(logits, target, grad_out) -> torch.Tensor:
+    lib = N.require()
+    bsz, o = logits.shape
+    dz = torch.empty_like(logits)
+    N.check(lib.dpb_cross_entropy_bwd(N.ptr(logits), N.ptr(target), N.ptr(grad_out), N.ptr(dz), bsz, o, N.stream()),
+            "dpb_cross_entropy_bwd")
+    N.count_launches(1)
+    return dz
+
+
+def sgd_step(p, g, m, n: int, lr: float, momentum: float, wd: float, grad_scale: float = 1.0,
+             nesterov: bool = False) -> None:
+    lib = N.require()
+    N.check(lib.dpb_sgd_step(N.ptr(p), N.ptr(g), N.ptr(m), n, lr, momentum, wd, grad_scale, int(nesterov),
+                             N.stream()), "dpb_sgd_step")
+    N.count_launches(1)

@@ -1,0 +1,270 @@
+"""Bucketed, backward-overlapped data parallelism: this framework's ``DistributedDataParallel``.
+
+Stands in for ``torch.nn.parallel.DistributedDataParallel(model)`` as the reference uses it with all defaults
+(main_ddp.py:137, main_part3.py:122; behaviour catalogued in SURVEY.md §3.4):
+
+* construction: parameter shapes are verified across ranks, then parameters and buffers are broadcast from rank 0;
+* every training forward: BatchNorm buffers are broadcast from rank 0 (``broadcast_buffers=True``);
+* backward: gradients are grouped into buckets in gradient-ready order (first bucket capped at 1 MiB, then 25 MiB; a
+  tensor that overflows the cap closes the bucket after being added -- for VGG-11 that gives the reference's rebuilt
+  layout of 9 461 800 / 27 157 504 / 305 152 bytes); when the last gradient of a bucket has been accumulated the bucket
+  is averaged (pre-divide by world size, SUM) while the rest of backward keeps running;
+* ``state_dict()`` keys carry the ``module.`` prefix.
+
+On CUDA the bucket *is* a contiguous range of the NVLink-symmetric gradient arena (the arena is laid out in
+gradient-ready order, so no copy-in / copy-out), the bucket planner and ready-count reducer are C++
+(``dpb_plan_buckets`` / ``dpb_reducer_*`` in libdpb200), and each bucket is reduced by the two-shot P2P kernel on a side
+stream, fenced with events against the main stream.  On CPU (gloo) the same planner drives flat-bucket async
+``all_reduce`` calls -- the oracle for tests.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from .. import _native as N
+from ..utils.arena import FlatArena
+from .comm import Communicator, SymmetricBuffer
+
+FIRST_BUCKET_BYTES = 1024 * 1024
+DEFAULT_BUCKET_MB = 25
+
+
+def expected_ready_order(module: nn.Module) -> List[int]:
+    """Indices into ``list(module.parameters())`` in the order their gradients become ready during backward.
+    The network is a chain, so modules finish in reverse; inside a module autograd produces weight then bias, except
+    for ``Linear`` (addmm) where the bias gradient comes first -- VGG-11: 33,32,30,31,28,29,...,2,3,0,1."""
+    index = {id(p): i for i, p in enumerate(module.parameters())}
+    order: List[int] = []
+    leaves = [m for m in module.modules() if len(list(m.parameters(recurse=False))) > 0]
+    for m in reversed(leaves):
+        ps = [p for _, p in m.named_parameters(recurse=False)]
+        if isinstance(m, nn.Linear):
+            ps = list(reversed(ps))
+        order.extend(index[id(p)] for p in ps)
+    return order
+
+
+def plan_buckets(bytes_in_ready_order: List[int], first_cap: int = FIRST_BUCKET_BYTES,
+                 cap: int = DEFAULT_BUCKET_MB * 1024 * 1024) -> List[int]:
+    """Bucket id per tensor (ready order).  C++ planner when the native library is loadable, same rule in Python
+    otherwise (CPU-only environments without nvcc)."""
+    n = len(bytes_in_ready_order)
+    lib = N.load(build_if_missing=False)
+    if lib is not None:
+        arr = (ctypes.c_longlong * n)(*bytes_in_ready_order)
+        out = (ctypes.c_int * n)()
+        lib.dpb_plan_buckets(n, arr, first_cap, cap, out)
+        return list(out)
+    ids, bucket, fill, limit = [], 0, 0, first_cap
+    for i, b in enumerate(bytes_in_ready_order):
+        ids.append(bucket)
+        fill += b
+        if fill >= limit and i + 1 < n:
+            bucket, fill, limit = bucket + 1, 0, cap
+    return ids
+
+
+class DistributedDataParallel(nn.Module):
+    def __init__(self, module: nn.Module, bucket_cap_mb: float = DEFAULT_BUCKET_MB, broadcast_buffers: bool = True,
+                 process_group=None, comm: Optional[Communicator] = None):
+        super().__init__()
+        self.module = module
+        self.process_group = process_group
+        self.broadcast_buffers = broadcast_buffers
+        self.world_size = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(process_group) if dist.is_initialized() else 0
+        self._params = list(module.parameters())
+        self._cuda = self._params[0].is_cuda
+        self._verify_shapes()
+
+        ready = expected_ready_order(module)
+        sizes = [self._params[i].numel() * 4 for i in ready]
+        bucket_ready = plan_buckets(sizes, FIRST_BUCKET_BYTES, int(bucket_cap_mb * 1024 * 1024))
+        self.ready_order = ready
+        self.bucket_of_param = [0] * len(self._params)
+        for pos, i in enumerate(ready):
+            self.bucket_of_param[i] = bucket_ready[pos]
+        self.num_buckets = max(bucket_ready) + 1
+        self.bucket_sizes = [sum(s for s, b in zip(sizes, bucket_ready) if b == k) for k in range(self.num_buckets)]
+
+        self._callback_queued = False
+        self._reducer = ctypes.c_void_p()
+        self.comm = comm
+        self._owns_comm = False
+        self._bufs: dict[str, SymmetricBuffer] = {}
+        self._buffer_block: Optional[SymmetricBuffer] = None
+        if self._cuda:
+            self._setup_cuda()
+        else:
+            self._pending = [0] * self.num_buckets
+            self._works = []
+        self._sync_module_states()
+        for i, p in enumerate(self._params):
+            if p.requires_grad:
+                p.register_post_accumulate_grad_hook(self._make_hook(i))
+
+    # ------------------------------------------------------------------------------------------------ set-up
+    def _verify_shapes(self) -> None:
+        if self.world_size == 1:
+            return
+        mine = [tuple(p.shape) for p in self._params]
+        allv = [None] * self.world_size
+        dist.all_gather_object(allv, mine, group=self.process_group)
+        for r, other in enumerate(allv):
+            if other != mine:
+                raise RuntimeError(f"DDP: parameter shapes on rank {r} differ from rank {self.rank}")
+
+    def _setup_cuda(self) -> None:
+        lib = N.require()
+        dev = self._params[0].device
+        if self.comm is None:
+            self.comm = Communicator(self.rank, self.world_size, dev, self.process_group)
+            self._owns_comm = True
+        if getattr(self.module, "_dpb_arena", None) is not None:
+            raise RuntimeError("wrap the model in DistributedDataParallel before any other arena adoption")
+
+        def allocator(numel: int, kind: str) -> torch.Tensor:
+            if kind in ("grad", "param"):
+                b = self.comm.alloc(numel)
+                self._bufs[kind] = b
+                return b.tensor
+            return torch.zeros(numel, device=dev, dtype=torch.float32)
+
+        # arena laid out in gradient-ready order => every bucket is one contiguous range
+        names = [n for n, _ in self.module.named_parameters()]
+        order = self.ready_order
+        self.arena = FlatArena([self._params[i] for i in order], [names[i] for i in order], allocator)
+        self.module._dpb_arena = self.arena
+        self._arena_pos = {i: pos for pos, i in enumerate(order)}
+        n = len(order)
+        offs = (ctypes.c_longlong * n)(*self.arena.offsets)
+        cnts = (ctypes.c_longlong * n)(*[(x + 63) // 64 * 64 for x in self.arena.numels])
+        bks = (ctypes.c_int * n)(*[self.bucket_of_param[i] for i in order])
+        N.check(lib.dpb_reducer_create(self.comm.handle, n, offs, cnts, bks, self.num_buckets,
+                                       self._bufs["grad"].table, 1.0 / self.world_size, ctypes.byref(self._reducer)),
+                "dpb_reducer_create")
+        # BatchNorm buffers into one symmetric block: floats first, then the int64 counters
+        fbufs = [(m, k, b) for m in self.module.modules() for k, b in m._buffers.items()
+                 if b is not None and b.dtype == torch.float32]
+        ibufs = [(m, k, b) for m in self.module.modules() for k, b in m._buffers.items()
+                 if b is not None and b.dtype == torch.int64]
+        fl = sum((b.numel() + 3) // 4 * 4 for _, _, b in fbufs)
+        il = sum((2 * b.numel() + 3) // 4 * 4 for _, _, b in ibufs)
+        if fl + il > 0:
+            blk = self.comm.alloc(fl + il)
+            off = 0
+            with torch.no_grad():
+                for m, k, b in fbufs:
+                    v = blk.tensor[off:off + b.numel()].view(b.shape)
+                    v.copy_(b)
+                    m._buffers[k] = v
+                    off += (b.numel() + 3) // 4 * 4
+                for m, k, b in ibufs:
+                    v = blk.tensor[off:off + 2 * b.numel()].view(torch.int64).view(b.shape)
+                    v.copy_(b)
+                    m._buffers[k] = v
+                    off += (2 * b.numel() + 3) // 4 * 4
+            self._buffer_block = blk
+
+    def _sync_module_states(self) -> None:
+        """Broadcast parameters and buffers from rank 0 (torch DDP's ``_sync_module_states``)."""
+        if self.world_size == 1:
+            return
+        if self._cuda:
+            self.comm.broadcast(self._bufs["param"], 0, self.arena.total, root=0)
+            if self._buffer_block is not None:
+                self.comm.broadcast(self._buffer_block, root=0)
+            torch.cuda.synchronize()
+        else:
+            with torch.no_grad():
+                for t in list(self.module.parameters()) + list(self.module.buffers()):
+                    dist.broadcast(t, src=0, group=self.process_group)
+
+    def _sync_buffers(self) -> None:
+        if self.world_size == 1:
+            return
+        if self._cuda:
+            if self._buffer_block is not None:
+                self.comm.broadcast(self._buffer_block, root=0)
+        else:
+            with torch.no_grad():
+                for b in self.module.buffers():
+                    dist.broadcast(b, src=0, group=self.process_group)
+
+    # ------------------------------------------------------------------------------------------------ forward/backward
+    def forward(self, *args, **kwargs):
+        if self.training and torch.is_grad_enabled():
+            if self.broadcast_buffers:
+                self._sync_buffers()
+            self._prepare_for_backward()
+        return self.module(*args, **kwargs)
+
+    def _prepare_for_backward(self) -> None:
+        self._callback_queued = False
+        if self._cuda:
+            N.check(N.require().dpb_reducer_prepare(self._reducer), "dpb_reducer_prepare")
+        else:
+            counts = [0] * self.num_buckets
+            for i, p in enumerate(self._params):
+                if p.requires_grad:
+                    counts[self.bucket_of_param[i]] += 1
+            self._pending = counts
+            self._works = []
+
+    def _make_hook(self, i: int):
+        def hook(param):
+            self._on_grad_ready(i, param)
+        return hook
+
+    def _on_grad_ready(self, i: int, param: torch.Tensor) -> None:
+        if not self._callback_queued:
+            torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
+            self._callback_queued = True
+        if self._cuda:
+            pos = self._arena_pos[i]
+            want = self.arena.grad_buf.data_ptr() + 4 * self.arena.offsets[pos]
+            if param.grad.data_ptr() != want:  # producer did not write in place: move it into the bucket memory
+                v = self.arena.grad_view(pos)
+                v.copy_(param.grad)
+                param.grad = v
+            N.check(N.require().dpb_reducer_mark_ready(self._reducer, pos, N.stream()), "dpb_reducer_mark_ready")
+            return
+        b = self.bucket_of_param[i]
+        self._pending[b] -= 1
+        if self._pending[b] == 0 and self.world_size > 1:
+            members = [j for j in self.ready_order if self.bucket_of_param[j] == b and self._params[j].grad is not None]
+            flat = torch.cat([self._params[j].grad.reshape(-1) for j in members]).div_(self.world_size)
+            work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.process_group, async_op=True)
+            self._works.append((work, flat, members))
+
+    def _finalize_backward(self) -> None:
+        if self._cuda:
+            lib = N.require()
+            launched = lib.dpb_reducer_launched(self._reducer)
+            N.check(lib.dpb_reducer_finalize(self._reducer, N.stream()), "dpb_reducer_finalize")
+            N.count_launches(launched)
+            return
+        for work, flat, members in self._works:
+            work.wait()
+            off = 0
+            with torch.no_grad():
+                for j in members:
+                    g = self._params[j].grad
+                    g.copy_(flat[off:off + g.numel()].view_as(g))
+                    off += g.numel()
+        self._works = []
+
+    def close(self) -> None:
+        if self._cuda:
+            torch.cuda.synchronize()
+            if self._reducer:
+                N.require().dpb_reducer_destroy(self._reducer)
+                self._reducer = ctypes.c_void_p()
+            if self._owns_comm and self.comm is not None:
+                self.comm.close()
+                self.comm = None
