@@ -39,6 +39,7 @@ struct ConvGemmParams {
   float* stat_sq;        // fprop only: [m_tiles][N_total]
   float* workspace;      // split-K partials: [tiles][splits][128*NT]
   unsigned int* counters;  // split-K arrival counters, one per tile, self-resetting
+  float* debug_dump;       // bring-up aid: CTA (0,0,0) copies its first stage (A then B, as laid out in smem) here
 };
 
 template <int NT, int STAGES>
@@ -133,28 +134,34 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           const int tap = kk / cpt, cc = kk - tap * cpt;
           const int r = tap / 3, sx = tap - 3 * r;
           tma_load_4d(sa, &mapA, &full_bar[s], cc * 32, a_w0 + sx - 1, a_h0 + r - 1, a_n0);
-          // weights viewed as (ci%32, co, (tap*Cin+ci)/32): rows = co (GEMM K), 128-byte row = 32 ci (GEMM N)
-          tma_load_3d(sb, &mapB, &full_bar[s], 0, cc * 32, ((8 - tap) * p.CinW + n_tile * NT) >> 5);
+          // MN-major B: one 32(co = GEMM K) x 32(ci = GEMM N) box of the KRSC weights per 32-wide N atom, flipped tap
+#pragma unroll
+          for (int a = 0; a < NT / 32; ++a)
+            tma_load_2d(sb + a * 4096, &mapB, &full_bar[s], (8 - tap) * p.CinW + n_tile * NT + a * 32, cc * 32);
         } else {
           const int r = wtap / 3, sx = wtap - 3 * r;
           const int p0 = kk * 32;
           const int w0 = p0 % p.W;
           const int h0 = (p0 / p.W) % p.H;
           const int n0 = p0 / (p.W * p.H);
-          // dY viewed as (co%32, pix, co/32)
-          tma_load_3d(sa, &mapA, &full_bar[s], 0, p0, m_tile * 4);
-          // X viewed as (ci%32, w, h, n, ci/32)
-          tma_load_5d(sb, &mapB, &full_bar[s], 0, w0 + sx - 1, h0 + r - 1, n0, n_tile * (NT / 32));
+          // MN-major A: 32 pixels (GEMM K) x 32 co per M atom;  MN-major B: 32 shifted pixels x 32 ci per N atom
+#pragma unroll
+          for (int a = 0; a < 4; ++a)
+            tma_load_2d(sa + a * 4096, &mapA, &full_bar[s], m_tile * 128 + a * 32, p0);
+#pragma unroll
+          for (int a = 0; a < NT / 32; ++a)
+            tma_load_4d(sb + a * 4096, &mapB, &full_bar[s], n_tile * NT + a * 32, w0 + sx - 1, h0 + r - 1, n0);
         }
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     constexpr uint32_t idesc = umma_idesc_tf32(NT, A_MN, B_MN);
-    // K-major SW128: 8-row groups 1024 B apart (SBO), LBO unused.  MN-major SW128: 32-element MN atoms are one
-    // 32-row x 128 B block (4096 B) apart (LBO), 8-row K groups 1024 B apart (SBO).
-    constexpr uint32_t a_lbo = A_MN ? 4096 : 16, a_sbo = 1024;
-    constexpr uint32_t b_lbo = B_MN ? 4096 : 16, b_sbo = 1024;
+    // K-major (SWIZZLE_128B): 8-row groups 1024 B apart (SBO), LBO unused.
+    // MN-major (SWIZZLE_128B_BASE32B): smem is [K rows][128 B of MN]; 4-row K groups 512 B apart (SBO), 32-element MN
+    // atoms one 32-row block (4096 B) apart (LBO).
+    constexpr uint32_t a_lbo = A_MN ? 4096 : 16, a_sbo = A_MN ? 512 : 1024, a_lt = A_MN ? 1 : 2;
+    constexpr uint32_t b_lbo = B_MN ? 4096 : 16, b_sbo = B_MN ? 512 : 1024, b_lt = B_MN ? 1 : 2;
     constexpr uint32_t a_kstep = A_MN ? 1024 : 32;  // bytes per UMMA k-step (8 tf32)
     constexpr uint32_t b_kstep = B_MN ? 1024 : 32;
     for (int i = 0; i < k_count; ++i) {
@@ -162,13 +169,18 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
       const uint32_t ph = (i / STAGES) & 1;
       mbar_wait(&full_bar[s], ph, 200 + s);
       tc_fence_after();
+      if (p.debug_dump != nullptr && i == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+        const float* src = reinterpret_cast<const float*>(stage_base);  // bring-up aid: raw stage 0 (A then B)
+        for (int j = lane; j < S::kStageBytes / 4; j += 32) p.debug_dump[j] = src[j];
+        __syncwarp();
+      }
       if (elect_one()) {
         const uint32_t sa = smem_u32(stage_base + s * S::kStageBytes);
         const uint32_t sb = sa + S::kABytes;
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {
-          const uint64_t ad = umma_smem_desc_sw128(sa + ks * a_kstep, a_lbo, a_sbo);
-          const uint64_t bd = umma_smem_desc_sw128(sb + ks * b_kstep, b_lbo, b_sbo);
+          const uint64_t ad = umma_smem_desc(sa + ks * a_kstep, a_lbo, a_sbo, a_lt);
+          const uint64_t bd = umma_smem_desc(sb + ks * b_kstep, b_lbo, b_sbo, b_lt);
           umma_tf32(tmem_acc, ad, bd, idesc, (i > 0 || ks > 0) ? 1u : 0u);
         }
         umma_commit(&empty_bar[s]);              // frees the smem slot when these MMAs retire

@@ -27,17 +27,23 @@ inline PFN_encodeTiled get_encode_tiled() {
 
 // fp32 tensor map, SWIZZLE_128B, zero fill out of bounds.  dims/strides innermost first; strides[i] is the byte pitch
 // of dimension i+1.
+// mn_major: the box feeds an MN-major tf32 UMMA operand, whose only legal shared-memory layout is the 128-byte
+// swizzle with a 32-byte atom (UMMA layout type SWIZZLE_128B_BASE32B <-> TMA SWIZZLE_128B_ATOM_32B).
 inline int make_map_f32(CUtensorMap* map, const void* base, int rank, const cuuint64_t* dims,
-                        const cuuint64_t* strides_bytes, const cuuint32_t* box) {
+                        const cuuint64_t* strides_bytes, const cuuint32_t* box, bool mn_major = false) {
   PFN_encodeTiled enc = get_encode_tiled();
   if (!enc) return set_error(-10, "cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
   cuuint32_t estr[5] = {1, 1, 1, 1, 1};
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(base), dims,
-                   strides_bytes, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   strides_bytes, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return set_error(-11, "cuTensorMapEncodeTiled failed (rank %d, CUresult %d)", rank, (int)r);
   return 0;
 }
+
+// bring-up aid, set through dpb_debug_set_conv_dump()
+inline float* g_conv_debug_dump = nullptr;
 
 struct ConvGeom {
   int n, h, w, cin, cout;
@@ -114,6 +120,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
   p.H = g.h; p.W = g.w; p.NImg = g.n; p.CinW = g.cin;
   p.bias = bias; p.stat_sum = stat_sum; p.stat_sq = stat_sq; p.workspace = workspace; p.counters = counters;
   p.out = out;
+  p.debug_dump = g_conv_debug_dump;
   CUtensorMap mA, mB;
   dim3 grid;
   int nt;
@@ -146,10 +153,10 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
       cuuint32_t box[2] = {32, (cuuint32_t)nt};
       if ((rc = make_map_f32(&mB, w, 2, dims, str, box))) return rc;
     } else {
-      cuuint64_t dims[3] = {32, (cuuint64_t)g.cout, (cuuint64_t)(9 * g.cin / 32)};
-      cuuint64_t str[2] = {(cuuint64_t)9 * g.cin * 4, 128};
-      cuuint32_t box[3] = {32, 32, (cuuint32_t)(nt / 32)};
-      if ((rc = make_map_f32(&mB, w, 3, dims, str, box))) return rc;
+      cuuint64_t dims[2] = {(cuuint64_t)9 * g.cin, (cuuint64_t)g.cout};
+      cuuint64_t str[1] = {(cuuint64_t)9 * g.cin * 4};
+      cuuint32_t box[2] = {32, 32};
+      if ((rc = make_map_f32(&mB, w, 2, dims, str, box, true))) return rc;
     }
     grid = dim3(m_tiles, n_tiles, p.splits);
     if (out_m_tiles) *out_m_tiles = m_tiles;
@@ -170,16 +177,16 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
   const int n_tiles = g.cin / nt;
   p.splits = pick_splits(m_tiles * n_tiles * 9, p.k_iters, nt, splits_override);
   {
-    cuuint64_t dims[3] = {32, (cuuint64_t)pixels, (cuuint64_t)(g.cout / 32)};
-    cuuint64_t str[2] = {(cuuint64_t)g.cout * 4, 128};
-    cuuint32_t box[3] = {32, 32, 4};
-    if ((rc = make_map_f32(&mA, in, 3, dims, str, box))) return rc;
+    cuuint64_t dims[2] = {(cuuint64_t)g.cout, (cuuint64_t)pixels};
+    cuuint64_t str[1] = {(cuuint64_t)g.cout * 4};
+    cuuint32_t box[2] = {32, 32};
+    if ((rc = make_map_f32(&mA, in, 2, dims, str, box, true))) return rc;
   }
   {
-    cuuint64_t dims[5] = {32, (cuuint64_t)g.w, (cuuint64_t)g.h, (cuuint64_t)g.n, (cuuint64_t)(g.cin / 32)};
-    cuuint64_t str[4] = {(cuuint64_t)g.cin * 4, (cuuint64_t)g.w * g.cin * 4, (cuuint64_t)g.h * g.w * g.cin * 4, 128};
-    cuuint32_t box[5] = {32, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn, (cuuint32_t)(nt / 32)};
-    if ((rc = make_map_f32(&mB, in2, 5, dims, str, box))) return rc;
+    cuuint64_t dims[4] = {(cuuint64_t)g.cin, (cuuint64_t)g.w, (cuuint64_t)g.h, (cuuint64_t)g.n};
+    cuuint64_t str[3] = {(cuuint64_t)g.cin * 4, (cuuint64_t)g.w * g.cin * 4, (cuuint64_t)g.h * g.w * g.cin * 4};
+    cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
+    if ((rc = make_map_f32(&mB, in2, 4, dims, str, box, true))) return rc;
   }
   grid = dim3(m_tiles, n_tiles, 9 * p.splits);
   if (out_m_tiles) *out_m_tiles = m_tiles;

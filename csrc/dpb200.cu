@@ -42,6 +42,11 @@ int dpb_last_device_error(int* out5) {
   return 0;
 }
 
+int dpb_debug_set_conv_dump(void* buf) {
+  g_conv_debug_dump = reinterpret_cast<float*>(buf);
+  return 0;
+}
+
 size_t dpb_conv_workspace_bytes(void) { return kConvWorkspaceBytes; }
 size_t dpb_conv_counter_bytes(void) { return (size_t)kConvCounterSlots * sizeof(unsigned int); }
 

@@ -72,6 +72,7 @@ _SIGNATURES = {
     "dpb_version": (c_int, []),
     "dpb_last_error": (c_char_p, []),
     "dpb_last_device_error": (c_int, [POINTER(c_int)]),
+    "dpb_debug_set_conv_dump": (c_int, [_P]),
     "dpb_conv_workspace_bytes": (c_size_t, []),
     "dpb_conv_counter_bytes": (c_size_t, []),
     "dpb_conv3x3_gemm": (c_int, [_I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, POINTER(c_int), _P]),

@@ -26,6 +26,9 @@ const char* dpb_last_error(void);
 /* Diagnostic left behind by a kernel that gave up (pipeline or peer-signal timeout). out[5] = code, where, block,
  * aux0, aux1.  Clears the record. */
 int dpb_last_device_error(int* out5);
+/* Bring-up aid: when buf != NULL, CTA (0,0,0) of every tensor-core conv launch copies its first pipeline stage
+ * (A tile then B tile, as laid out in shared memory; up to 48 KiB) to buf. NULL switches it off. */
+int dpb_debug_set_conv_dump(void* buf);
 /* Scratch needed by the tensor-core convolution (split-K partial tiles + arrival counters). */
 size_t dpb_conv_workspace_bytes(void);
 size_t dpb_conv_counter_bytes(void);

@@ -1,0 +1,131 @@
+"""Memory-bound sm_100a kernels against plain PyTorch fp32 CPU references of the same op."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def K():
+    from distributed_pytorch_b200 import _native
+    _native.require()
+    from distributed_pytorch_b200.ops import kernels
+    return kernels
+
+
+def nhwc(t):
+    return t.contiguous(memory_format=torch.channels_last)
+
+
+def test_sgd_kernel_matches_torch(K):
+    torch.manual_seed(0)
+    for n in (10, 4096 + 3, 1 << 20):
+        p = torch.randn(n)
+        ref = torch.nn.Parameter(p.clone())
+        opt = torch.optim.SGD([ref], lr=0.1, momentum=0.9, weight_decay=1e-4)
+        pd, md = p.cuda(), torch.zeros(n).cuda()
+        for _ in range(3):
+            g = torch.randn(n)
+            ref.grad = g.clone()
+            opt.step()
+            K.sgd_step(pd, g.cuda(), md, n, 0.1, 0.9, 1e-4)
+        assert torch.allclose(pd.cpu(), ref.detach(), rtol=1e-5, atol=1e-6)
+        assert torch.allclose(md.cpu(), opt.state[ref]["momentum_buffer"], rtol=1e-5, atol=1e-6)
+
+
+def test_linear_and_cross_entropy(K):
+    torch.manual_seed(1)
+    for B in (1, 32, 80, 256):
+        x = torch.randn(B, 512, requires_grad=True)
+        w = torch.randn(10, 512, requires_grad=True) * 0.05
+        w.retain_grad()
+        b = torch.randn(10, requires_grad=True)
+        y = torch.randint(0, 10, (B,))
+        logits = F.linear(x, w, b)
+        loss = F.cross_entropy(logits, y)
+        loss.backward()
+        xd, wd, bd, yd = x.detach().cuda(), w.detach().cuda(), b.detach().cuda(), y.cuda()
+        out = K.linear_fwd(xd, wd, bd)
+        assert torch.allclose(out.cpu(), logits.detach(), rtol=1e-4, atol=1e-4)
+        metrics = torch.zeros(2, device="cuda")
+        l = K.cross_entropy_fwd(out, yd, metrics)
+        assert torch.allclose(l.cpu(), loss.detach(), rtol=1e-5, atol=1e-5)
+        assert int(metrics[1].item()) == int((logits.argmax(1) == y).sum())
+        dz = K.cross_entropy_bwd(out, yd, torch.ones((), device="cuda"))
+        dx, dw, db = torch.empty_like(xd), torch.empty_like(wd), torch.empty_like(bd)
+        K.linear_bwd(dz, xd, wd, dx, dw, db)
+        assert torch.allclose(dx.cpu(), x.grad, rtol=1e-4, atol=1e-6)
+        assert torch.allclose(dw.cpu(), w.grad, rtol=1e-4, atol=1e-5)
+        assert torch.allclose(db.cpu(), b.grad, rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("N,C,H,pool", [(4, 64, 32, True), (3, 128, 16, True), (5, 256, 8, False), (32, 512, 2, True),
+                                        (7, 512, 4, False)])
+def test_bn_relu_pool_forward_backward(K, N, C, H, pool):
+    torch.manual_seed(2)
+    y = torch.randn(N, C, H, H) * 1.5 + 0.3
+    gamma = torch.rand(C) + 0.5
+    beta = torch.randn(C) * 0.2
+    rm, rv = torch.zeros(C), torch.ones(C)
+    yr = y.clone().requires_grad_(True)
+    g_, b_ = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    z = F.relu(F.batch_norm(yr, rm, rv, g_, b_, True, 0.1, 1e-5))
+    if pool:
+        z = F.max_pool2d(z, 2, 2)
+    dout = torch.randn_like(z)
+    z.backward(dout)
+    # device: stats as the conv epilogue would leave them (per 128-pixel tile partials)
+    yd = nhwc(y.cuda())
+    flat = yd.permute(0, 2, 3, 1).reshape(-1, C)
+    tiles = (flat.shape[0] + 127) // 128
+    pad = torch.zeros(tiles * 128, C, device="cuda")
+    pad[: flat.shape[0]] = flat
+    ps = pad.view(tiles, 128, C).sum(1).contiguous()
+    pq = (pad * pad).view(tiles, 128, C).sum(1).contiguous()
+    rmd, rvd = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    nbt = torch.zeros((), dtype=torch.int64, device="cuda")
+    stats = K.bn_finalize(ps, pq, tiles, C, float(N * H * H), gamma.cuda(), beta.cuda(), rmd, rvd, nbt, 0.1, 1e-5)
+    out = K.bn_relu_pool_fwd(yd, stats[0], stats[1], pool)
+    assert out.shape == z.shape
+    assert torch.allclose(out.cpu(), z.detach(), rtol=1e-4, atol=1e-4)
+    assert torch.allclose(rmd.cpu(), rm, rtol=1e-4, atol=1e-5) and torch.allclose(rvd.cpu(), rv, rtol=1e-4, atol=1e-5)
+    assert int(nbt.item()) == 1
+    dg, db, dcb = torch.empty(C, device="cuda"), torch.empty(C, device="cuda"), torch.ones(C, device="cuda")
+    dy = K.bn_relu_pool_bwd(yd, nhwc(dout.cuda()), stats, gamma.cuda(), dg, db, dcb, pool)
+    scale = max(1.0, float(yr.grad.abs().max()))
+    assert torch.allclose(dy.cpu(), yr.grad, rtol=2e-3, atol=2e-4 * scale)
+    assert torch.allclose(dg.cpu(), g_.grad, rtol=2e-3, atol=2e-3)
+    assert torch.allclose(db.cpu(), b_.grad, rtol=2e-3, atol=2e-3)
+    assert float(dcb.abs().max()) == 0.0
+
+
+def test_bn_eval_mode(K):
+    torch.manual_seed(3)
+    C = 128
+    y = torch.randn(2, C, 8, 8)
+    gamma, beta, rm, rv = torch.rand(C) + 0.5, torch.randn(C), torch.randn(C) * 0.1, torch.rand(C) + 0.5
+    ref = F.max_pool2d(F.relu(F.batch_norm(y, rm, rv, gamma, beta, False, 0.1, 1e-5)), 2, 2)
+    st = K.bn_eval_scale_shift(C, gamma.cuda(), beta.cuda(), rm.cuda(), rv.cuda(), 1e-5)
+    out = K.bn_relu_pool_fwd(nhwc(y.cuda()), st[0], st[1], True)
+    assert torch.allclose(out.cpu(), ref, rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("N", [1, 8, 33])
+def test_first_conv_fprop_and_wgrad(K, N):
+    torch.manual_seed(4)
+    x = torch.randn(N, 3, 32, 32)
+    w = (torch.randn(64, 3, 3, 3) * 0.2).requires_grad_(True)
+    b = torch.randn(64)
+    ref = F.conv2d(x, w, b, padding=1)
+    dy = torch.randn_like(ref)
+    ref.backward(dy)
+    wd = nhwc(w.detach().cuda())
+    y = torch.empty((N, 64, 32, 32), device="cuda").contiguous(memory_format=torch.channels_last)
+    ps, pq, parts = K.first_conv_fprop(x.cuda(), wd, b.cuda(), y, True)
+    assert torch.allclose(y.cpu(), ref.detach(), rtol=1e-4, atol=1e-4)
+    assert torch.allclose(ps.sum(0).cpu(), ref.detach().sum((0, 2, 3)), rtol=1e-3, atol=1e-2)
+    assert torch.allclose(pq.sum(0).cpu(), (ref.detach() ** 2).sum((0, 2, 3)), rtol=1e-3, atol=1e-2)
+    dw = torch.empty_like(wd)
+    K.first_conv_wgrad(x.cuda(), nhwc(dy.cuda()), dw)
+    assert torch.allclose(dw.cpu(), w.grad, rtol=1e-3, atol=1e-3 * float(w.grad.abs().max()))
