@@ -266,10 +266,25 @@ PeerPtrs make_ptrs(void* const* bufs, int n) {
   return p;
 }
 
+// Largest grid.x the launch may use: real ranks are bounded by the signal-pad geometry, emulated ranks additionally by
+// co-residency of the cooperative launch (all virtual ranks' CTAs must fit on the one GPU at once).
+template <typename K>
+int comm_block_cap(dpb_comm* c, K kern_emu, int threads) {
+  if (!c->emulate) return kCommMaxBlocks;
+  int per_sm = 0, dev = 0, sms = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern_emu, threads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  int cap = per_sm * sms / c->ctx.nranks;
+  if (cap > kCommMaxBlocks) cap = kCommMaxBlocks;
+  return cap < 1 ? 1 : cap;
+}
+
 template <typename K, typename... Args>
 int launch_comm(dpb_comm* c, K kern_real, K kern_emu, int blocks, int threads, cudaStream_t st, Args... args) {
+  const int cap = comm_block_cap(c, kern_emu, threads);
   if (blocks < 1) blocks = 1;
-  if (blocks > kCommMaxBlocks) blocks = kCommMaxBlocks;
+  if (blocks > cap) blocks = cap;
   if (!c->emulate) {
     kern_real<<<blocks, threads, 0, st>>>(args...);
     DPB_CUDA(cudaGetLastError());
@@ -354,7 +369,7 @@ int dpb_allreduce(dpb_comm* c, int channel, void* const* bufs, long long offset,
   if (algo == 0) algo = (n4 * 16 <= (256 << 10)) ? 1 : 2;  // <= 256 KiB: one-shot
   if (algo == 1) {
     int b = (int)((n4 + 512LL * U - 1) / (512LL * U));
-    if (b <= kCommMaxBlocks) {
+    if (b <= comm_block_cap(c, allreduce_oneshot_kernel<true, U>, 512)) {  // the whole range must fit one grid pass
       PeerPtrs d = make_ptrs(bufs, c->ctx.nranks);
       return launch_comm(c, allreduce_oneshot_kernel<false, U>, allreduce_oneshot_kernel<true, U>, b, 512, S(stream),
                          c->ctx, channel, d, offset / 4, n4, scale);
