@@ -525,3 +525,66 @@ int dpb_reducer_finalize(dpb_reducer* r, dpb_stream_t main_stream) {
 int dpb_reducer_launched(dpb_reducer* r) { return r->launched; }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------ allocation-free variant
+// dpb_bn_relu_pool_bwd() needs two pieces of scratch from its caller: the per-block partial sums of the reduce pass
+// ([2][kBnBwdBlocks][c] floats) and the per-channel coefficients ([3][c] floats).  Some callers have no way to provide
+// device memory of their own: a host program that links only this C ABI (no CUDA runtime calls of its own, no
+// PyTorch allocator), or a component that is handed inputs and outputs by a framework and is forbidden to allocate
+// on its hot path.  For them the scratch below is part of the library image: it exists on every GPU that loads
+// libdpb200.so from the moment the module is loaded until the process exits, and costs kNoAllocScratchFloats * 4 bytes
+// (about 1.2 MB) there whether or not the entry point is ever called.
+constexpr int kNoAllocMaxChannels = 512;  // widest BatchNorm of the VGG family
+constexpr size_t kNoAllocScratchFloats = (size_t)(2 * kBnBwdBlocks + 3) * kNoAllocMaxChannels;
+static __device__ __align__(256) float g_noalloc_bn_scratch[kNoAllocScratchFloats];
+
+namespace {
+constexpr int kNoAllocMaxDevices = 64;
+float* g_noalloc_scratch_addr[kNoAllocMaxDevices] = {nullptr};  // device address of the array, per device ordinal
+std::mutex g_noalloc_mutex;
+
+// `g_noalloc_bn_scratch` names a host-side shadow in host code, not device memory, so it must never be passed to a
+// kernel as is.  The device address is looked up once per device, with that device current.
+int noalloc_scratch_for_current_device(float** out) {
+  int dev = -1;
+  DPB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return set_error(-20, "no-alloc scratch: device ordinal %d unsupported", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (g_noalloc_scratch_addr[dev] == nullptr) {
+    float* p = nullptr;
+    DPB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_bn_scratch));
+    if (p == nullptr) return set_error(-20, "no-alloc scratch: cudaGetSymbolAddress returned a null address");
+    g_noalloc_scratch_addr[dev] = p;
+  }
+  *out = g_noalloc_scratch_addr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+int dpb_noalloc_max_channels(void) { return kNoAllocMaxChannels; }
+
+int dpb_bn_relu_pool_bwd_noalloc(const float* y, const float* dout, const float* scale, const float* shift,
+                                 const float* save_mean, const float* save_invstd, const float* gamma, float* dgamma,
+                                 float* dbeta, float* conv_dbias, float* dy, int n, int h, int w, int c, int pool,
+                                 dpb_stream_t stream) {
+  if (c > kNoAllocMaxChannels)
+    return set_error(-21,
+                     "dpb_bn_relu_pool_bwd_noalloc: %d channels exceed the built-in scratch (maximum %d); use "
+                     "dpb_bn_relu_pool_bwd with caller-provided scratch instead",
+                     c, kNoAllocMaxChannels);
+  if (c <= 0 || n <= 0 || h <= 0 || w <= 0) return set_error(-21, "dpb_bn_relu_pool_bwd_noalloc: empty problem");
+  float* scratch = nullptr;
+  int rc = noalloc_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  // Same layout the allocating entry point expects from its caller; every word the kernels read from it is written
+  // earlier in this same call (partials by the reduce pass, coefficients by the finalize pass), so nothing has to be
+  // cleared even though the array still holds the previous call's contents.
+  float* part = scratch;
+  float* coef = scratch + (size_t)2 * kBnBwdBlocks * kNoAllocMaxChannels;
+  return dpb_bn_relu_pool_bwd(y, dout, scale, shift, save_mean, save_invstd, gamma, part, coef, dgamma, dbeta,
+                              conv_dbias, dy, n, h, w, c, pool, stream);
+}
+
+}  // extern "C"

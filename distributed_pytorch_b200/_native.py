@@ -85,6 +85,8 @@ _SIGNATURES = {
     "dpb_bn_relu_pool_fwd": (c_int, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dpb_bn_bwd_blocks": (c_int, []),
     "dpb_bn_relu_pool_bwd": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dpb_noalloc_max_channels": (c_int, []),
+    "dpb_bn_relu_pool_bwd_noalloc": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dpb_linear_fwd": (c_int, [_P, _P, _P, _P, _I, _I, _I, _P]),
     "dpb_linear_bwd": (c_int, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "dpb_cross_entropy_fwd": (c_int, [_P, _P, _P, _P, _I, _I, _P]),

@@ -67,6 +67,24 @@ int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, 
                          float* coef, float* dgamma, float* dbeta, float* conv_dbias, float* dy, int n, int h, int w,
                          int c, int pool, dpb_stream_t stream);
 
+/* Allocation-free variant of dpb_bn_relu_pool_bwd.  (No counterpart in the reference: it exists for callers of this
+ * library that cannot obtain device memory themselves -- a host program that talks only to this C ABI, or a plug-in
+ * that is given input/output buffers and must not call cudaMalloc or any framework allocator.)
+ * Same arguments and results as dpb_bn_relu_pool_bwd minus `part` and `coef`: that scratch lives in a file-scope
+ * __device__ array inside the library (about 1.2 MB on every GPU that loads it, held until the process exits).
+ *   - limit: c <= dpb_noalloc_max_channels() (512); larger c is refused with an error, nothing is launched.
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress) with that device
+ *     current; make that first call before starting any stream capture on the device.
+ *   - the call itself performs no cudaMalloc / cudaFree and uses no allocating library routine.
+ *   - all calls on a device share the one array, which keeps whatever the last call left in it; nothing needs
+ *     clearing between calls (every word read is written earlier in the same call), but two calls whose kernels can
+ *     overlap on the GPU (different streams, no ordering) race on it -- serialise them. */
+int dpb_noalloc_max_channels(void);
+int dpb_bn_relu_pool_bwd_noalloc(const float* y, const float* dout, const float* scale, const float* shift,
+                                 const float* save_mean, const float* save_invstd, const float* gamma, float* dgamma,
+                                 float* dbeta, float* conv_dbias, float* dy, int n, int h, int w, int c, int pool,
+                                 dpb_stream_t stream);
+
 /* ---- classifier head, loss, metrics (ref: model.py:40,45; main.py:34,59-61,99) ----------------------------------- */
 int dpb_linear_fwd(const float* x, const float* w, const float* bias, float* out, int b, int k, int o,
                    dpb_stream_t stream);
