@@ -14,19 +14,20 @@
 namespace dpb {
 
 // ------------------------------------------------------------------------------------------------ forward finalize
-// grid = C/32 blocks of (32, 8) threads.  Partials are combined in double, in a fixed order.
+// grid = C/32 blocks of (32, 32) threads.  Partials are combined in double, in a fixed order.
 __global__ void bn_finalize_kernel(const float* __restrict__ part_sum, const float* __restrict__ part_sq, int T, int C,
                                    double count, const float* __restrict__ gamma, const float* __restrict__ beta,
                                    float* __restrict__ running_mean, float* __restrict__ running_var,
                                    long long* __restrict__ num_batches_tracked, float momentum, float eps,
                                    float* __restrict__ scale, float* __restrict__ shift, float* __restrict__ save_mean,
                                    float* __restrict__ save_invstd) {
-  __shared__ double s_sum[8][33], s_sq[8][33];
+  __shared__ double s_sum[32][33], s_sq[32][33];
   const int cx = threadIdx.x, ry = threadIdx.y;
   const int c = blockIdx.x * 32 + cx;
   double a = 0.0, b = 0.0;
   if (c < C) {
-    for (int t = ry; t < T; t += 8) {
+#pragma unroll 4
+    for (int t = ry; t < T; t += 32) {
       a += (double)part_sum[(size_t)t * C + c];
       b += (double)part_sq[(size_t)t * C + c];
     }
@@ -37,7 +38,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ part_sum, const flo
   if (ry == 0 && c < C) {
     double sum = 0.0, sq = 0.0;
 #pragma unroll
-    for (int r = 0; r < 8; ++r) {
+    for (int r = 0; r < 32; ++r) {
       sum += s_sum[r][cx];
       sq += s_sq[r][cx];
     }
@@ -209,19 +210,20 @@ bn_bwd_reduce_kernel(const float* __restrict__ y, const float* __restrict__ dout
   }
 }
 
-// grid = C/32 blocks of (32, 8).  Writes dgamma, dbeta, the preceding conv's bias gradient (optionally accumulating into existing values is the caller's
+// grid = C/32 blocks of (32, 32).  Writes dgamma, dbeta, the preceding conv's bias gradient (optionally accumulating into existing values is the caller's
 // business: these are plain stores) and the three per-channel coefficients of dY = a*g + k1*y + k0.
 __global__ void bn_bwd_finalize_kernel(const float* __restrict__ part_g, const float* __restrict__ part_gx, int T,
                                        int C, double count, const float* __restrict__ gamma,
                                        const float* __restrict__ mean, const float* __restrict__ invstd,
                                        float* __restrict__ dgamma, float* __restrict__ dbeta,
                                        float* __restrict__ conv_dbias, float* __restrict__ coef /* [3][C] */) {
-  __shared__ double s_a[8][33], s_b[8][33];
+  __shared__ double s_a[32][33], s_b[32][33];
   const int cx = threadIdx.x, ry = threadIdx.y;
   const int c = blockIdx.x * 32 + cx;
   double a = 0.0, b = 0.0;
   if (c < C) {
-    for (int t = ry; t < T; t += 8) {
+#pragma unroll 4
+    for (int t = ry; t < T; t += 32) {
       a += (double)part_g[(size_t)t * C + c];
       b += (double)part_gx[(size_t)t * C + c];
     }
@@ -232,7 +234,7 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ part_g, const f
   if (ry == 0 && c < C) {
     double sg = 0.0, sgx = 0.0;
 #pragma unroll
-    for (int r = 0; r < 8; ++r) {
+    for (int r = 0; r < 32; ++r) {
       sg += s_a[r][cx];
       sgx += s_b[r][cx];
     }

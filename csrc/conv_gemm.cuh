@@ -13,9 +13,9 @@
 // Tile: 128 (M) x NT (N) per CTA, K consumed in chunks of 32 tf32 (one 128-byte swizzle row), 4 UMMA k-steps of 8.
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer, warps 2..5 =
 // epilogue (TMEM -> registers -> smem transpose -> coalesced 128-byte global rows).
-// Split-K: every split writes its fp32 partial tile to a workspace; the CTA that arrives last on the tile's counter
-// reduces the partials in split order (deterministic), applies the bias and emits the per-channel sum / sum-of-squares
-// partials that the BatchNorm finalize kernel consumes.
+// Split-K: every split writes its fp32 partial tile to a workspace; splitk_reduce_kernel then sums the partials in split
+// order (deterministic) with the whole GPU, applies the bias and emits the per-channel sum / sum-of-squares partials that
+// the BatchNorm finalize kernel consumes.
 #pragma once
 #include <cuda.h>
 #include "ptx.cuh"
@@ -69,7 +69,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   uint64_t* empty_bar = bars + STAGES;     // [STAGES]
   uint64_t* acc_bar = bars + 2 * STAGES;   // [1]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
-  uint32_t* last_flag = tmem_slot + 1;
   float* colred = reinterpret_cast<float*>(smem + STAGES * S::kStageBytes + S::kStagingBytes + S::kBarBytes);
 
   const int warp = threadIdx.x >> 5;
@@ -260,66 +259,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           p.stat_sq[(size_t)m_tile * p.N_total + n_tile * NT + c] = s1;
         }
       }
-    } else {
-      // split-K: publish partial, last arriver reduces
-      __threadfence();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (et == 0) {
-        const unsigned int old = atomicAdd(&p.counters[tile_id], 1u);
-        *last_flag = (old == (unsigned)p.splits - 1) ? 1u : 0u;
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (*last_flag) {
-        __threadfence();
-        const float* wsb = p.workspace + (size_t)tile_id * p.splits * (size_t)(128 * NT);
-        constexpr int C4 = NT / 4;          // float4 columns per row
-        constexpr int RG = 128 / C4 > 0 ? 128 / C4 : 1;  // row groups covered by the 128 threads at once
-        const int c4 = et % C4;
-        const int rg = et / C4;
-        float4 ssum = make_float4(0.f, 0.f, 0.f, 0.f), ssq = make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        const int colb = n_tile * NT + c4 * 4;
-        if (MODE == kFprop && p.bias != nullptr) b4 = *reinterpret_cast<const float4*>(p.bias + colb);
-        if (rg < RG) {
-          for (int r = rg; r < 128; r += RG) {
-            const int grow = m_tile * 128 + r;
-            if (grow >= p.M_total) break;
-            float4 acc = b4;
-            for (int sp = 0; sp < p.splits; ++sp) {
-              const float4 t = __ldcg(reinterpret_cast<const float4*>(wsb + (size_t)sp * (128 * NT) + (size_t)r * NT) + c4);
-              acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
-            }
-            float* orow;
-            if (MODE == kWgrad)
-              orow = p.out + (size_t)grow * p.out_ld + (size_t)wtap * p.CinW + colb;
-            else
-              orow = p.out + (size_t)grow * p.out_ld + colb;
-            *reinterpret_cast<float4*>(orow) = acc;
-            ssum.x += acc.x; ssum.y += acc.y; ssum.z += acc.z; ssum.w += acc.w;
-            ssq.x += acc.x * acc.x; ssq.y += acc.y * acc.y; ssq.z += acc.z * acc.z; ssq.w += acc.w * acc.w;
-          }
-        }
-        if (MODE == kFprop && p.stat_sum != nullptr) {
-          // reduce the RG row groups per column through smem (staging is free now: 4*32*33 floats >= 2*128*4... )
-          float* red = staging;  // [RG][2][NT]
-          if (rg < RG) {
-            *reinterpret_cast<float4*>(red + ((size_t)rg * 2 + 0) * NT + c4 * 4) = ssum;
-            *reinterpret_cast<float4*>(red + ((size_t)rg * 2 + 1) * NT + c4 * 4) = ssq;
-          }
-          asm volatile("bar.sync 1, 128;" ::: "memory");
-          for (int c = et; c < NT; c += 128) {
-            float s0 = 0.f, s1 = 0.f;
-            for (int g = 0; g < RG; ++g) {
-              s0 += red[((size_t)g * 2 + 0) * NT + c];
-              s1 += red[((size_t)g * 2 + 1) * NT + c];
-            }
-            p.stat_sum[(size_t)m_tile * p.N_total + n_tile * NT + c] = s0;
-            p.stat_sq[(size_t)m_tile * p.N_total + n_tile * NT + c] = s1;
-          }
-        }
-        if (et == 0) p.counters[tile_id] = 0u;  // re-arm for the next launch (graph replays included)
-      }
     }
+    // split-K: the partial tile is in the workspace; splitk_reduce_kernel (next launch) finishes the job
   }
 
   tc_fence_before();
@@ -327,6 +268,62 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc<NT>(tmem_acc);
+  }
+}
+
+// Second phase of split-K.  grid = (tiles, NT/32, 4): one block sums a 32-row x 32-column piece of one output tile over
+// all splits (fixed order), adds the bias, stores 128-byte row segments and leaves one BatchNorm partial row per
+// (m_tile, 32-row piece): stat row index = m_tile * 4 + blockIdx.z.   block = (32 columns, 8 row lanes).
+template <int MODE>
+__global__ void __launch_bounds__(256)
+splitk_reduce_kernel(const ConvGemmParams p, int NT, int m_tiles, int n_tiles) {
+  __shared__ float red[2][8][33];
+  const int tile_id = blockIdx.x;
+  const int m_tile = tile_id % m_tiles;
+  const int n_tile = (tile_id / m_tiles) % n_tiles;
+  const int wtap = tile_id / (m_tiles * n_tiles);
+  const int cx = threadIdx.x, ry = threadIdx.y;
+  const int col_in_tile = blockIdx.y * 32 + cx;
+  const int col = n_tile * NT + col_in_tile;
+  const float* wsb = p.workspace + (size_t)tile_id * p.splits * (size_t)(128 * NT);
+  const size_t split_stride = (size_t)128 * NT;
+  float b = 0.f;
+  if (MODE == kFprop && p.bias != nullptr) b = p.bias[col];
+  float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = blockIdx.z * 32 + ry * 4 + i;
+    const int grow = m_tile * 128 + r;
+    if (grow < p.M_total) {
+      const float* src = wsb + (size_t)r * NT + col_in_tile;
+      float acc = b;
+      int sp = 0;
+      for (; sp + 4 <= p.splits; sp += 4) {
+        const float t0 = __ldcg(src + (size_t)(sp + 0) * split_stride);
+        const float t1 = __ldcg(src + (size_t)(sp + 1) * split_stride);
+        const float t2 = __ldcg(src + (size_t)(sp + 2) * split_stride);
+        const float t3 = __ldcg(src + (size_t)(sp + 3) * split_stride);
+        acc += t0; acc += t1; acc += t2; acc += t3;
+      }
+      for (; sp < p.splits; ++sp) acc += __ldcg(src + (size_t)sp * split_stride);
+      float* dst = (MODE == kWgrad) ? p.out + (size_t)grow * p.out_ld + (size_t)wtap * p.CinW + col
+                                    : p.out + (size_t)grow * p.out_ld + col;
+      *dst = acc;
+      s0 += acc;
+      s1 += acc * acc;
+    }
+  }
+  if (MODE == kFprop && p.stat_sum != nullptr) {
+    red[0][ry][cx] = s0;
+    red[1][ry][cx] = s1;
+    __syncthreads();
+    if (ry < 2) {
+      float a = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) a += red[ry][k][cx];
+      float* dst = ry == 0 ? p.stat_sum : p.stat_sq;
+      dst[(size_t)(m_tile * 4 + blockIdx.z) * p.N_total + col] = a;
+    }
   }
 }
 

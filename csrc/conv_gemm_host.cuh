@@ -44,6 +44,8 @@ inline int make_map_f32(CUtensorMap* map, const void* base, int rank, const cuui
 
 // bring-up aid, set through dpb_debug_set_conv_dump()
 inline float* g_conv_debug_dump = nullptr;
+// kernels launched by the most recent conv_gemm_dispatch on this thread (1, or 2 with the split-K reduce)
+inline thread_local int g_conv_last_launches = 0;
 
 struct ConvGeom {
   int n, h, w, cin, cout;
@@ -69,6 +71,13 @@ int launch_conv_gemm_nt(const CUtensorMap& mA, const CUtensorMap& mB, const Conv
   }
   kern<<<grid, 192, S::kTotal, stream>>>(mA, mB, p);
   DPB_CUDA(cudaGetLastError());
+  g_conv_last_launches = p.splits > 1 ? 2 : 1;
+  if (p.splits > 1) {
+    const int m_tiles = grid.x, n_tiles = grid.y;
+    const int tiles = m_tiles * n_tiles * (MODE == kWgrad ? 9 : 1);
+    splitk_reduce_kernel<MODE><<<dim3(tiles, NT / 32, 4), dim3(32, 8), 0, stream>>>(p, NT, m_tiles, n_tiles);
+    DPB_CUDA(cudaGetLastError());
+  }
   return 0;
 }
 
@@ -140,7 +149,6 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
     const int m_tiles = (int)((pixels + 127) / 128);
     const int n_tiles = cn / nt;
     p.splits = pick_splits(m_tiles * n_tiles, p.k_iters, nt, splits_override);
-    if (m_tiles * n_tiles > kConvCounterSlots && p.splits > 1) p.splits = 1;
     {
       cuuint64_t dims[4] = {(cuuint64_t)ck, (cuuint64_t)g.w, (cuuint64_t)g.h, (cuuint64_t)g.n};
       cuuint64_t str[3] = {(cuuint64_t)ck * 4, (cuuint64_t)g.w * ck * 4, (cuuint64_t)g.h * g.w * ck * 4};
@@ -159,7 +167,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
       if ((rc = make_map_f32(&mB, w, 2, dims, str, box, true))) return rc;
     }
     grid = dim3(m_tiles, n_tiles, p.splits);
-    if (out_m_tiles) *out_m_tiles = m_tiles;
+    if (out_m_tiles) *out_m_tiles = p.splits > 1 ? 4 * m_tiles : m_tiles;  // BatchNorm partial rows written
     if (mode == kFprop) return launch_conv_gemm_mode<kFprop>(nt, mA, mB, p, grid, stream);
     return launch_conv_gemm_mode<kDgrad>(nt, mA, mB, p, grid, stream);
   }

@@ -47,6 +47,8 @@ int dpb_debug_set_conv_dump(void* buf) {
   return 0;
 }
 
+int dpb_conv_last_launches(void) { return g_conv_last_launches; }
+
 size_t dpb_conv_workspace_bytes(void) { return kConvWorkspaceBytes; }
 size_t dpb_conv_counter_bytes(void) { return (size_t)kConvCounterSlots * sizeof(unsigned int); }
 
@@ -78,7 +80,7 @@ int dpb_first_conv_wgrad_blocks(void) { return kFirstWgradBlocks; }
 int dpb_first_conv_wgrad(const float* x, const float* dy, float* partials, float* dw, int n, int h, int w,
                          dpb_stream_t stream) {
   const long long pix = (long long)n * h * w;
-  int blocks = (int)((pix + 63) / 64);
+  int blocks = (int)((pix + 15) / 16);
   if (blocks > kFirstWgradBlocks) blocks = kFirstWgradBlocks;
   first_conv_wgrad_kernel<<<blocks, 256, 0, S(stream)>>>(x, dy, partials, n, h, w);
   DPB_CUDA(cudaGetLastError());
@@ -93,7 +95,7 @@ int dpb_bn_finalize(const float* part_sum, const float* part_sq, int parts, int 
                     const float* beta, float* running_mean, float* running_var, long long* nbt, float momentum,
                     float eps, float* scale, float* shift, float* save_mean, float* save_invstd,
                     dpb_stream_t stream) {
-  bn_finalize_kernel<<<(c + 31) / 32, dim3(32, 8), 0, S(stream)>>>(part_sum, part_sq, parts, c, count, gamma, beta,
+  bn_finalize_kernel<<<(c + 31) / 32, dim3(32, 32), 0, S(stream)>>>(part_sum, part_sq, parts, c, count, gamma, beta,
                                                                    running_mean, running_var, nbt, momentum, eps,
                                                                    scale, shift, save_mean, save_invstd);
   DPB_CUDA(cudaGetLastError());
@@ -146,7 +148,7 @@ int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, 
                                                                   part_g, part_gx, opix, c4, h, w);
   DPB_CUDA(cudaGetLastError());
   const double count = (double)n * h * w;
-  bn_bwd_finalize_kernel<<<(c + 31) / 32, dim3(32, 8), 0, S(stream)>>>(part_g, part_gx, blocks, c, count, gamma,
+  bn_bwd_finalize_kernel<<<(c + 31) / 32, dim3(32, 32), 0, S(stream)>>>(part_g, part_gx, blocks, c, count, gamma,
                                                                        save_mean, save_invstd, dgamma, dbeta, conv_dbias,
                                                                        coef);
   DPB_CUDA(cudaGetLastError());
@@ -164,7 +166,7 @@ int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, 
 int dpb_linear_fwd(const float* x, const float* w, const float* bias, float* out, int b, int k, int o,
                    dpb_stream_t stream) {
   if (o > kMaxClasses) return set_error(-3, "linear: out_features %d > %d", o, kMaxClasses);
-  linear_fwd_kernel<<<(b * 32 + 255) / 256, 256, 0, S(stream)>>>(x, w, bias, out, b, k, o);
+  linear_fwd_kernel<<<(b * 32 + 127) / 128, 128, 0, S(stream)>>>(x, w, bias, out, b, k, o);
   DPB_CUDA(cudaGetLastError());
   return 0;
 }

@@ -20,11 +20,13 @@ __global__ void __launch_bounds__(256)
 first_conv_fprop_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                         float* __restrict__ y, float* __restrict__ part_sum, float* __restrict__ part_sq, int N, int H,
                         int W) {
-  __shared__ __align__(16) float w_s[27 * 64];   // [k][co]
+  // [k][channel group][16 + 4 pad]: the four channel groups of a warp read four different 16-byte bank groups
+  // (with a dense [k][64] layout groups 0/2 and 1/3 collide: ncu showed 4 extra wavefronts per LDS.128)
+  __shared__ __align__(16) float w_s[27 * 80];
   __shared__ float red[8][2][64];
   for (int i = threadIdx.x; i < 27 * 64; i += 256) {
     const int co = i & 63, k = i >> 6;
-    w_s[i] = w[co * 27 + k];
+    w_s[k * 80 + (co >> 4) * 20 + (co & 15)] = w[co * 27 + k];
   }
   __syncthreads();
   const int cg = threadIdx.x & 3;       // 16-channel group
@@ -62,7 +64,7 @@ first_conv_fprop_kernel(const float* __restrict__ x, const float* __restrict__ w
       for (int j = 0; j < 16; ++j) acc[j] = bsv[j];
 #pragma unroll
       for (int k = 0; k < 27; ++k) {
-        const float4* wr = reinterpret_cast<const float4*>(w_s + k * 64 + cg * 16);
+        const float4* wr = reinterpret_cast<const float4*>(w_s + k * 80 + cg * 20);
 #pragma unroll
         for (int j4 = 0; j4 < 4; ++j4) {
           const float4 wv = wr[j4];
@@ -109,52 +111,69 @@ first_conv_fprop_kernel(const float* __restrict__ x, const float* __restrict__ w
 }
 
 // dy: [N*H*W][64], x: NCHW.  partials: [gridDim.x][64*27] laid out like dW (co*27 + tap*3 + ci).
+// Register-blocked: a thread owns 4 output channels x 27 taps (108 accumulators); per pixel it loads one float4 of dY
+// and the 27 patch values (the same address for the 16 threads of a pixel lane: broadcast from L1), i.e. 4 FMAs per
+// load.  (The first version kept the patch in shared memory and issued one LDS per FMA: 186 us at batch 256.)
 __global__ void __launch_bounds__(256)
 first_conv_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ partials, int N,
                         int H, int W) {
-  __shared__ float patch[64][28];
   __shared__ float red[4][64 * 27];  // 27.6 KB
-  const int co = threadIdx.x & 63;
-  const int qd = threadIdx.x >> 6;  // pixel quarter
+  const int cg = threadIdx.x & 15;   // output channels 4cg .. 4cg+3
+  const int pl = threadIdx.x >> 4;   // 16 pixel lanes
   const long long total = (long long)N * H * W;
-  const long long HW = (long long)H * W;
-  float acc[27];
+  const int HW = H * W;
+  float acc[27][4];
 #pragma unroll
-  for (int k = 0; k < 27; ++k) acc[k] = 0.f;
-  for (long long base = (long long)blockIdx.x * 64; base < total; base += (long long)gridDim.x * 64) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < 64 * 27; i += 256) {
-      const int pl = i / 27, k = i - pl * 27;
-      const long long pix = base + pl;
-      float v = 0.f;
-      if (pix < total) {
-        const int n = (int)(pix / HW);
-        const int hw = (int)(pix - n * HW);
-        const int h = hw / W, wc = hw - h * W;
-        const int tap = k / 3, ci = k - tap * 3;
-        const int r = tap / 3, s = tap - r * 3;
+  for (int k = 0; k < 27; ++k) { acc[k][0] = 0.f; acc[k][1] = 0.f; acc[k][2] = 0.f; acc[k][3] = 0.f; }
+  const float4* dy4 = reinterpret_cast<const float4*>(dy);
+  for (long long pix = (long long)blockIdx.x * 16 + pl; pix < total; pix += (long long)gridDim.x * 16) {
+    const int n = (int)(pix / HW);
+    const int hw = (int)(pix - (long long)n * HW);
+    const int h = hw / W, wc = hw - h * W;
+    const float4 g = __ldg(dy4 + pix * 16 + cg);
+    const float* xb = x + (long long)n * 3 * HW + hw;   // channel 0, centre tap
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
         const int hh = h + r - 1, ww = wc + s - 1;
-        if (hh >= 0 && hh < H && ww >= 0 && ww < W) v = __ldg(x + ((long long)(n * 3 + ci) * H + hh) * W + ww);
-      }
-      patch[pl][k] = v;
-    }
-    __syncthreads();
-#pragma unroll 4
-    for (int j = 0; j < 16; ++j) {
-      const int pl = qd * 16 + j;
-      const long long pix = base + pl;
-      if (pix < total) {
-        const float g = __ldg(dy + pix * 64 + co);
+        const bool ok = (hh >= 0) && (hh < H) && (ww >= 0) && (ww < W);
+        const int off = (r - 1) * W + (s - 1);
 #pragma unroll
-        for (int k = 0; k < 27; ++k) acc[k] = fmaf(g, patch[pl][k], acc[k]);
+        for (int ci = 0; ci < 3; ++ci) {
+          const float xv = ok ? __ldg(xb + ci * HW + off) : 0.f;
+          const int k = (r * 3 + s) * 3 + ci;
+          acc[k][0] = fmaf(g.x, xv, acc[k][0]);
+          acc[k][1] = fmaf(g.y, xv, acc[k][1]);
+          acc[k][2] = fmaf(g.z, xv, acc[k][2]);
+          acc[k][3] = fmaf(g.w, xv, acc[k][3]);
+        }
       }
     }
   }
+  // pixel lanes 2w and 2w+1 live in the two half-warps of warp w
 #pragma unroll
-  for (int k = 0; k < 27; ++k) red[qd][co * 27 + k] = acc[k];
+  for (int k = 0; k < 27; ++k)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[k][j] += __shfl_xor_sync(0xffffffffu, acc[k][j], 16);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // fixed-order combine of the 8 warps: warps 0-3 store, warps 4-7 add on top, then the 4 slots are summed
+  if (warp < 4 && lane < 16) {
+#pragma unroll
+    for (int k = 0; k < 27; ++k)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) red[warp][(cg * 4 + j) * 27 + k] = acc[k][j];
+  }
+  __syncthreads();
+  if (warp >= 4 && lane < 16) {
+#pragma unroll
+    for (int k = 0; k < 27; ++k)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) red[warp - 4][(cg * 4 + j) * 27 + k] += acc[k][j];
+  }
   __syncthreads();
   for (int i = threadIdx.x; i < 64 * 27; i += 256)
-    partials[(size_t)blockIdx.x * (64 * 27) + i] = red[0][i] + red[1][i] + red[2][i] + red[3][i];
+    partials[(size_t)blockIdx.x * (64 * 27) + i] = (red[0][i] + red[1][i]) + (red[2][i] + red[3][i]);
 }
 
 // out[c] = sum_t partials[t][c], fixed order.  grid = ceil(n/32) blocks of (32, 8).

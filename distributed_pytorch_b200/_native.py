@@ -76,6 +76,7 @@ _SIGNATURES = {
     "dpb_conv_workspace_bytes": (c_size_t, []),
     "dpb_conv_counter_bytes": (c_size_t, []),
     "dpb_conv3x3_gemm": (c_int, [_I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, POINTER(c_int), _P]),
+    "dpb_conv_last_launches": (c_int, []),
     "dpb_first_conv_blocks": (c_int, [_I, _I, _I]),
     "dpb_first_conv_fprop": (c_int, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "dpb_first_conv_wgrad_blocks": (c_int, []),

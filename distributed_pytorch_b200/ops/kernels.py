@@ -69,14 +69,14 @@ def conv3x3_gemm(mode: int, n: int, h: int, w: int, cin: int, cout: int, inp: to
     stat_sum = stat_sq = None
     m_tiles = ctypes.c_int(0)
     if want_stats:
-        tiles = (n * h * w + 127) // 128
+        tiles = 4 * ((n * h * w + 127) // 128)  # split-K leaves 4 partial rows per 128-pixel tile, else 1
         stat_sum = torch.empty((tiles, cout), device=out.device, dtype=torch.float32)
         stat_sq = torch.empty((tiles, cout), device=out.device, dtype=torch.float32)
     N.check(lib.dpb_conv3x3_gemm(mode, n, h, w, cin, cout, N.ptr(inp), N.ptr(inp2), N.ptr(weight), N.ptr(out),
                                  N.ptr(bias), N.ptr(stat_sum), N.ptr(stat_sq), N.ptr(sc.conv_ws),
                                  N.ptr(sc.conv_counters), nt, splits, ctypes.byref(m_tiles), N.stream()),
             "dpb_conv3x3_gemm")
-    N.count_launches(1)
+    N.count_launches(lib.dpb_conv_last_launches())
     if want_stats:
         return stat_sum, stat_sq, m_tiles.value
     return None
