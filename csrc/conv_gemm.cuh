@@ -47,9 +47,14 @@ struct ConvGemmSmem {
   static constexpr int kABytes = 128 * 128;  // 128 rows x 32 tf32
   static constexpr int kBBytes = NT * 128;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStagingBytes = 4 * 32 * 33 * 4;  // per-epilogue-warp 32x33 fp32 transpose tile
+  // The epilogue's per-warp 32x33 fp32 transpose tiles (4 * 32 * 33 * 4 = 16.5 KB) reuse stage 0: by the time the
+  // accumulator barrier fires every TMA load has landed and every MMA has finished reading shared memory.  Keeping the
+  // footprint at ~100 KB (NT <= 128) lets two CTAs share an SM, so one CTA's prologue / epilogue overlaps the other's
+  // main loop.
+  static constexpr int kStagingBytes = 4 * 32 * 33 * 4;
+  static_assert(kStagingBytes <= kStageBytes, "staging must fit in one pipeline stage");
   static constexpr int kBarBytes = 256;
-  static constexpr int kTotal = 1024 /*align slack*/ + STAGES * kStageBytes + kStagingBytes + kBarBytes + 2 * NT * 4 * 4;
+  static constexpr int kTotal = 1024 /*align slack*/ + STAGES * kStageBytes + kBarBytes + 2 * NT * 4 * 4;
 };
 
 template <int MODE, int NT, int STAGES>
@@ -63,13 +68,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* stage_base = smem;
-  float* staging = reinterpret_cast<float*>(smem + STAGES * S::kStageBytes);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * S::kStageBytes + S::kStagingBytes);
+  float* staging = reinterpret_cast<float*>(smem);  // aliases stage 0, used only after the main loop has drained
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * S::kStageBytes);
   uint64_t* full_bar = bars;               // [STAGES]
   uint64_t* empty_bar = bars + STAGES;     // [STAGES]
   uint64_t* acc_bar = bars + 2 * STAGES;   // [1]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
-  float* colred = reinterpret_cast<float*>(smem + STAGES * S::kStageBytes + S::kStagingBytes + S::kBarBytes);
+  float* colred = reinterpret_cast<float*>(smem + STAGES * S::kStageBytes + S::kBarBytes);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -268,62 +273,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc<NT>(tmem_acc);
-  }
-}
-
-// Second phase of split-K.  grid = (tiles, NT/32, 4): one block sums a 32-row x 32-column piece of one output tile over
-// all splits (fixed order), adds the bias, stores 128-byte row segments and leaves one BatchNorm partial row per
-// (m_tile, 32-row piece): stat row index = m_tile * 4 + blockIdx.z.   block = (32 columns, 8 row lanes).
-template <int MODE>
-__global__ void __launch_bounds__(256)
-splitk_reduce_kernel(const ConvGemmParams p, int NT, int m_tiles, int n_tiles) {
-  __shared__ float red[2][8][33];
-  const int tile_id = blockIdx.x;
-  const int m_tile = tile_id % m_tiles;
-  const int n_tile = (tile_id / m_tiles) % n_tiles;
-  const int wtap = tile_id / (m_tiles * n_tiles);
-  const int cx = threadIdx.x, ry = threadIdx.y;
-  const int col_in_tile = blockIdx.y * 32 + cx;
-  const int col = n_tile * NT + col_in_tile;
-  const float* wsb = p.workspace + (size_t)tile_id * p.splits * (size_t)(128 * NT);
-  const size_t split_stride = (size_t)128 * NT;
-  float b = 0.f;
-  if (MODE == kFprop && p.bias != nullptr) b = p.bias[col];
-  float s0 = 0.f, s1 = 0.f;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int r = blockIdx.z * 32 + ry * 4 + i;
-    const int grow = m_tile * 128 + r;
-    if (grow < p.M_total) {
-      const float* src = wsb + (size_t)r * NT + col_in_tile;
-      float acc = b;
-      int sp = 0;
-      for (; sp + 4 <= p.splits; sp += 4) {
-        const float t0 = __ldcg(src + (size_t)(sp + 0) * split_stride);
-        const float t1 = __ldcg(src + (size_t)(sp + 1) * split_stride);
-        const float t2 = __ldcg(src + (size_t)(sp + 2) * split_stride);
-        const float t3 = __ldcg(src + (size_t)(sp + 3) * split_stride);
-        acc += t0; acc += t1; acc += t2; acc += t3;
-      }
-      for (; sp < p.splits; ++sp) acc += __ldcg(src + (size_t)sp * split_stride);
-      float* dst = (MODE == kWgrad) ? p.out + (size_t)grow * p.out_ld + (size_t)wtap * p.CinW + col
-                                    : p.out + (size_t)grow * p.out_ld + col;
-      *dst = acc;
-      s0 += acc;
-      s1 += acc * acc;
-    }
-  }
-  if (MODE == kFprop && p.stat_sum != nullptr) {
-    red[0][ry][cx] = s0;
-    red[1][ry][cx] = s1;
-    __syncthreads();
-    if (ry < 2) {
-      float a = 0.f;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) a += red[ry][k][cx];
-      float* dst = ry == 0 ? p.stat_sum : p.stat_sq;
-      dst[(size_t)(m_tile * 4 + blockIdx.z) * p.N_total + col] = a;
-    }
   }
 }
 

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <mutex>
 #include "conv_gemm.cuh"
+#include "splitk_reduce.cuh"
 #include "errors.cuh"
 
 namespace dpb {
@@ -61,7 +62,7 @@ inline void pixel_box(int h, int w, int pixels, int* bw, int* bh, int* bn) {
 template <int MODE, int NT>
 int launch_conv_gemm_nt(const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
                         cudaStream_t stream) {
-  constexpr int STAGES = (NT == 256) ? 4 : 4;
+  constexpr int STAGES = (NT == 128) ? 3 : 4;  // NT 64: 4 x 24 KB, NT 128: 3 x 32 KB (two CTAs per SM); NT 256: 4 x 48 KB
   using S = ConvGemmSmem<NT, STAGES>;
   auto kern = conv_gemm_kernel<MODE, NT, STAGES>;
   static bool attr_set = false;  // per instantiation
@@ -75,7 +76,7 @@ int launch_conv_gemm_nt(const CUtensorMap& mA, const CUtensorMap& mB, const Conv
   if (p.splits > 1) {
     const int m_tiles = grid.x, n_tiles = grid.y;
     const int tiles = m_tiles * n_tiles * (MODE == kWgrad ? 9 : 1);
-    splitk_reduce_kernel<MODE><<<dim3(tiles, NT / 32, 4), dim3(32, 8), 0, stream>>>(p, NT, m_tiles, n_tiles);
+    splitk_reduce_kernel<MODE><<<dim3(tiles, 4), 256, 0, stream>>>(p, NT, m_tiles, n_tiles);
     DPB_CUDA(cudaGetLastError());
   }
   return 0;
@@ -96,14 +97,16 @@ constexpr size_t kConvWorkspaceBytes = (size_t)48 << 20;  // split-K partial til
 constexpr int kConvCounterSlots = 8192;
 
 // Number of CTAs we aim for: two waves of single-tile CTAs on 148 SMs.
-constexpr int kTargetCtas = 296;
+// Tunables (dpb_set_tuning): CTA count the split-K heuristic aims for, and the N tile used when the GEMM N extent allows it.
+inline int g_tune_target_ctas = 296;
+inline int g_tune_wide_nt = 128;
 
 inline int pick_splits(int tiles, int k_iters, int nt, int forced) {
   int splits = 1;
   if (forced > 0) {
     splits = forced;
-  } else if (tiles < kTargetCtas) {
-    splits = kTargetCtas / tiles;
+  } else if (tiles < g_tune_target_ctas) {
+    splits = g_tune_target_ctas / tiles;
     int max_by_k = k_iters / 4;  // keep >= 4 k-iterations (128 of K) per split
     if (max_by_k < 1) max_by_k = 1;
     if (splits > max_by_k) splits = max_by_k;
@@ -137,7 +140,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
   if (mode == kFprop || mode == kDgrad) {
     const int ck = (mode == kFprop) ? g.cin : g.cout;   // GEMM K channels
     const int cn = (mode == kFprop) ? g.cout : g.cin;   // GEMM N channels
-    nt = nt_override > 0 ? nt_override : (cn >= 128 ? 128 : 64);
+    nt = nt_override > 0 ? nt_override : (cn % g_tune_wide_nt == 0 ? g_tune_wide_nt : (cn >= 128 ? 128 : 64));
     if (cn % nt) return set_error(-13, "N tile %d does not divide %d", nt, cn);
     int bw, bh, bn;
     pixel_box(g.h, g.w, 128, &bw, &bh, &bn);
@@ -172,7 +175,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
     return launch_conv_gemm_mode<kDgrad>(nt, mA, mB, p, grid, stream);
   }
   // wgrad
-  nt = nt_override > 0 ? nt_override : (g.cin >= 128 ? 128 : 64);
+  nt = nt_override > 0 ? nt_override : (g.cin % g_tune_wide_nt == 0 ? g_tune_wide_nt : (g.cin >= 128 ? 128 : 64));
   if (g.cin % nt) return set_error(-13, "N tile %d does not divide Cin %d", nt, g.cin);
   int bw, bh, bn;
   pixel_box(g.h, g.w, 32, &bw, &bh, &bn);

@@ -47,6 +47,12 @@ int dpb_debug_set_conv_dump(void* buf) {
   return 0;
 }
 
+int dpb_set_tuning(int key, int value) {
+  if (key == 0 && value >= 1) { g_tune_target_ctas = value; return 0; }
+  if (key == 1 && (value == 64 || value == 128 || value == 256)) { g_tune_wide_nt = value; return 0; }
+  return set_error(-30, "dpb_set_tuning: bad key/value %d/%d", key, value);
+}
+
 int dpb_conv_last_launches(void) { return g_conv_last_launches; }
 
 size_t dpb_conv_workspace_bytes(void) { return kConvWorkspaceBytes; }
@@ -64,7 +70,8 @@ int dpb_conv3x3_gemm(int mode, int n, int h, int w, int cin, int cout, const flo
 
 int dpb_first_conv_blocks(int n, int h, int w) {
   const long long pix = (long long)n * h * w;
-  return (int)((pix + kFirstConvPixPerBlock - 1) / kFirstConvPixPerBlock);
+  const long long b = (pix + 15) / 16;
+  return (int)(b < kFirstConvMaxBlocks ? b : kFirstConvMaxBlocks);
 }
 
 int dpb_first_conv_fprop(const float* x, const float* weight, const float* bias, float* y, float* part_sum,

@@ -77,6 +77,7 @@ _SIGNATURES = {
     "dpb_conv_counter_bytes": (c_size_t, []),
     "dpb_conv3x3_gemm": (c_int, [_I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, POINTER(c_int), _P]),
     "dpb_conv_last_launches": (c_int, []),
+    "dpb_set_tuning": (c_int, [_I, _I]),
     "dpb_first_conv_blocks": (c_int, [_I, _I, _I]),
     "dpb_first_conv_fprop": (c_int, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "dpb_first_conv_wgrad_blocks": (c_int, []),
@@ -134,6 +135,9 @@ def load(build_if_missing: bool = True):
                 build()
             lib = ctypes.CDLL(LIB_PATH)
             _bind(lib)
+            for key, env in ((0, "DPB_CONV_TARGET_CTAS"), (1, "DPB_CONV_NT")):
+                if os.environ.get(env):
+                    lib.dpb_set_tuning(key, int(os.environ[env]))
             _lib = lib
             _load_error = None
         except Exception as exc:  # noqa: BLE001 - reported through load_error()/require()
