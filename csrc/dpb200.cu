@@ -69,13 +69,19 @@ int dpb_conv3x3_gemm(int mode, int n, int h, int w, int cin, int cout, const flo
 }
 
 int dpb_first_conv_blocks(int n, int h, int w) {
-  const long long pix = (long long)n * h * w;
-  const long long b = (pix + 15) / 16;
+  (void)w;
+  const long long b = (long long)n * ((h + kFcRows - 1) / kFcRows);  // tiles of kFcRows image rows
   return (int)(b < kFirstConvMaxBlocks ? b : kFirstConvMaxBlocks);
+}
+
+static int first_conv_check(int w) {
+  if (w < 2 || (w & 1) || w > kFcMaxW) return set_error(-7, "first conv: image width must be even and <= %d (got %d)", kFcMaxW, w);
+  return 0;
 }
 
 int dpb_first_conv_fprop(const float* x, const float* weight, const float* bias, float* y, float* part_sum,
                          float* part_sq, int n, int h, int w, dpb_stream_t stream) {
+  if (int rc = first_conv_check(w)) return rc;
   const int blocks = dpb_first_conv_blocks(n, h, w);
   first_conv_fprop_kernel<<<blocks, 256, 0, S(stream)>>>(x, weight, bias, y, part_sum, part_sq, n, h, w);
   DPB_CUDA(cudaGetLastError());
@@ -86,8 +92,8 @@ int dpb_first_conv_wgrad_blocks(void) { return kFirstWgradBlocks; }
 
 int dpb_first_conv_wgrad(const float* x, const float* dy, float* partials, float* dw, int n, int h, int w,
                          dpb_stream_t stream) {
-  const long long pix = (long long)n * h * w;
-  int blocks = (int)((pix + 15) / 16);
+  if (int rc = first_conv_check(w)) return rc;
+  int blocks = dpb_first_conv_blocks(n, h, w);
   if (blocks > kFirstWgradBlocks) blocks = kFirstWgradBlocks;
   first_conv_wgrad_kernel<<<blocks, 256, 0, S(stream)>>>(x, dy, partials, n, h, w);
   DPB_CUDA(cudaGetLastError());
