@@ -17,6 +17,7 @@
 using namespace dpb;
 
 namespace {
+int g_tune_comm_blocks = 64;  // default grid cap of the collective kernels (dpb_set_tuning key 2)
 inline cudaStream_t S(dpb_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 constexpr int kBnBwdBlocks = 296;
 constexpr int kFirstWgradBlocks = 296;
@@ -50,6 +51,7 @@ int dpb_debug_set_conv_dump(void* buf) {
 int dpb_set_tuning(int key, int value) {
   if (key == 0 && value >= 1) { g_tune_target_ctas = value; return 0; }
   if (key == 1 && (value == 64 || value == 128 || value == 256)) { g_tune_wide_nt = value; return 0; }
+  if (key == 2 && value >= 1 && value <= kCommMaxBlocks) { g_tune_comm_blocks = value; return 0; }
   return set_error(-30, "dpb_set_tuning: bad key/value %d/%d", key, value);
 }
 
@@ -314,7 +316,7 @@ int launch_comm(dpb_comm* c, K kern_real, K kern_emu, int blocks, int threads, c
 int comm_blocks_for(long long n4, int threads, int u, int want) {
   if (want > 0) return want > kCommMaxBlocks ? kCommMaxBlocks : want;
   long long b = (n4 + (long long)threads * u - 1) / ((long long)threads * u);
-  if (b > 64) b = 64;
+  if (b > g_tune_comm_blocks) b = g_tune_comm_blocks;
   if (b < 1) b = 1;
   return (int)b;
 }

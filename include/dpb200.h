@@ -42,7 +42,8 @@ int dpb_conv3x3_gemm(int mode, int n, int h, int w, int cin, int cout, const flo
                      const float* weight, float* out, const float* bias, float* stat_sum, float* stat_sq,
                      void* workspace, void* counters, int nt, int splits, int* m_tiles_out, dpb_stream_t stream);
 /* Heuristic knobs of the tensor-core conv. key 0: CTA count split-K aims for (default 296); key 1: preferred N tile
- * (64 / 128 / 256, default 128) when it divides the GEMM N extent. */
+ * (64 / 128 / 256, default 128) when it divides the GEMM N extent; key 2: default grid cap of the collective kernels
+ * (default 64, at most 128). */
 int dpb_set_tuning(int key, int value);
 /* Kernels launched by the calling thread's most recent dpb_conv3x3_gemm (1, or 2 when split-K adds its reduce). */
 int dpb_conv_last_launches(void);
