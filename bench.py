@@ -48,7 +48,67 @@ def parse_args(argv=None):
 
 # ---------------------------------------------------------------------------------------------------- clocks
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """SM clock and throttle reasons DURING the timed region (B200_PROFILING.md recipe).  Polls NVML every few
+    milliseconds from a thread (the timed region of a fast run is shorter than nvidia-smi's sampling period); falls
+    back to an `nvidia-smi -lms` subprocess when NVML cannot be loaded."""
+
+    def __init__(self, gpu_index: int, period_s: float = 0.004):
+        self.gpu, self.period = gpu_index, period_s
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thread = None
+        self._fallback = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception:  # noqa: BLE001 - any NVML problem -> nvidia-smi
+            self._nv = None
+            self._fallback = _SmiClockSampler(gpu_index)
+
+    def _poll(self):
+        nv = self._nv
+        names = (("hw_slowdown", "nvmlClocksEventReasonHwSlowdown", "nvmlClocksThrottleReasonHwSlowdown"),
+                 ("hw_thermal_slowdown", "nvmlClocksEventReasonHwThermalSlowdown", "nvmlClocksThrottleReasonHwThermalSlowdown"),
+                 ("sw_thermal_slowdown", "nvmlClocksEventReasonSwThermalSlowdown", "nvmlClocksThrottleReasonSwThermalSlowdown"),
+                 ("sw_power_cap", "nvmlClocksEventReasonSwPowerCap", "nvmlClocksThrottleReasonSwPowerCap"))
+        masks = [(n, getattr(nv, a, None) or getattr(nv, b, 0)) for n, a, b in names]
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or getattr(
+            nv, "nvmlDeviceGetCurrentClocksThrottleReasons", None)
+        while not self._stop.is_set():
+            try:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                if get_reasons is not None:
+                    r = int(get_reasons(self._h))
+                    for n, m in masks:
+                        if m and (r & m):
+                            self.reasons.add(n)
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(self.period)
+
+    def start(self):
+        if self._fallback is not None:
+            return self._fallback.start()
+        self._thread = threading.Thread(target=self._poll, daemon=True)
+        self._thread.start()
+
+    def stop(self) -> dict:
+        if self._fallback is not None:
+            return self._fallback.stop()
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join(timeout=2)
+        sm = self.samples
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.max_mhz, "samples": len(sm),
+                "reasons": sorted(self.reasons), "source": "nvml"}
+
+
+class _SmiClockSampler:
+    """nvidia-smi clocks / throttle reasons (fallback sampler)."""
 
     FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
               "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"

@@ -21,6 +21,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ part_sum, const flo
                                    long long* __restrict__ num_batches_tracked, float momentum, float eps,
                                    float* __restrict__ scale, float* __restrict__ shift, float* __restrict__ save_mean,
                                    float* __restrict__ save_invstd) {
+  pdl_prologue();
   __shared__ double s_sum[32][33], s_sq[32][33];
   const int cx = threadIdx.x, ry = threadIdx.y;
   const int c = blockIdx.x * 32 + cx;
@@ -65,6 +66,7 @@ __global__ void bn_eval_scale_shift_kernel(int C, const float* __restrict__ gamm
                                            const float* __restrict__ running_mean,
                                            const float* __restrict__ running_var, float eps, float* __restrict__ scale,
                                            float* __restrict__ shift) {
+  pdl_prologue();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float invstd = rsqrtf(running_var[c] + eps);
@@ -89,6 +91,7 @@ template <bool POOL>
 __global__ void __launch_bounds__(256)
 bn_relu_pool_fwd_kernel(const float* __restrict__ y, const float* __restrict__ scale, const float* __restrict__ shift,
                         float* __restrict__ out, long long out_units /* out pixels * C/4 */, int C4, int H, int W) {
+  pdl_prologue();
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < out_units; i += stride) {
     const int c4 = (int)(i % C4);
@@ -143,6 +146,7 @@ bn_bwd_reduce_kernel(const float* __restrict__ y, const float* __restrict__ dout
                      const float* __restrict__ shift, const float* __restrict__ mean,
                      const float* __restrict__ invstd, float* __restrict__ part_g, float* __restrict__ part_gx,
                      long long out_pixels, int C4, int H, int W) {
+  pdl_prologue();
   extern __shared__ float4 s_red[];  // [2][256]
   const int PL = 256 / C4;
   const int c4 = threadIdx.x % C4;
@@ -217,6 +221,7 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ part_g, const f
                                        const float* __restrict__ mean, const float* __restrict__ invstd,
                                        float* __restrict__ dgamma, float* __restrict__ dbeta,
                                        float* __restrict__ conv_dbias, float* __restrict__ coef /* [3][C] */) {
+  pdl_prologue();
   __shared__ double s_a[32][33], s_b[32][33];
   const int cx = threadIdx.x, ry = threadIdx.y;
   const int c = blockIdx.x * 32 + cx;
@@ -259,6 +264,7 @@ __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const float* __restrict__ y, const float* __restrict__ dout, const float* __restrict__ scale,
                     const float* __restrict__ shift, const float* __restrict__ coef, float* __restrict__ dy,
                     long long out_units, int C, int H, int W) {
+  pdl_prologue();
   const int C4 = C >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
   const float4* y4 = reinterpret_cast<const float4*>(y);

@@ -65,6 +65,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   constexpr bool B_MN = (MODE != kFprop);
   using S = ConvGemmSmem<NT, STAGES>;
 
+  pdl_launch_dependents();  // the next kernel may start its prologue; it waits for our completion itself
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* stage_base = smem;
@@ -110,6 +111,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (elect_one()) {
+      pdl_wait();  // inputs are produced by the previous kernel
       int a_w0 = 0, a_h0 = 0, a_n0 = 0;
       if (MODE != kWgrad) {
         // pixel box of this M tile
@@ -194,6 +196,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     }
   } else {
     // ------------------------------------------------------------------ epilogue warps (2..5)
+    pdl_wait();  // outputs / workspace may still be in use by the previous kernel
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     float* tile = staging + q * (32 * 33);
     const int row_base = m_tile * 128 + q * 32;

@@ -43,6 +43,23 @@ inline int make_map_f32(CUtensorMap* map, const void* base, int rank, const cuui
   return 0;
 }
 
+// Launch with programmatic stream serialization (see pdl_prologue in ptx.cuh); dpb_set_tuning key 4 switches it off.
+inline int g_tune_use_pdl = 0;  // measured: no gain inside CUDA graphs (1.074 vs 1.079 ms/step), so off by default
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = g_tune_use_pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 // bring-up aid, set through dpb_debug_set_conv_dump()
 inline float* g_conv_debug_dump = nullptr;
 // kernels launched by the most recent conv_gemm_dispatch on this thread (1, or 2 with the split-K reduce)
@@ -70,14 +87,13 @@ int launch_conv_gemm_nt(const CUtensorMap& mA, const CUtensorMap& mB, const Conv
     DPB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
     attr_set = true;
   }
-  kern<<<grid, 192, S::kTotal, stream>>>(mA, mB, p);
-  DPB_CUDA(cudaGetLastError());
+  DPB_CUDA(launch_k(kern, grid, dim3(192), S::kTotal, stream, mA, mB, p));
   g_conv_last_launches = p.splits > 1 ? 2 : 1;
   if (p.splits > 1) {
     const int m_tiles = grid.x, n_tiles = grid.y;
     const int tiles = m_tiles * n_tiles * (MODE == kWgrad ? 9 : 1);
-    splitk_reduce_kernel<MODE><<<dim3(tiles, 4), 256, 0, stream>>>(p, NT, m_tiles, n_tiles);
-    DPB_CUDA(cudaGetLastError());
+    const int pieces = splitk_pieces(tiles, m_tiles, NT);
+    DPB_CUDA(launch_k(splitk_reduce_kernel<MODE>, dim3(tiles, pieces), dim3(256), 0, stream, p, NT, m_tiles, n_tiles, pieces));
   }
   return 0;
 }
@@ -100,6 +116,7 @@ constexpr int kConvCounterSlots = 8192;
 // Tunables (dpb_set_tuning): CTA count the split-K heuristic aims for, and the N tile used when the GEMM N extent allows it.
 inline int g_tune_target_ctas = 296;
 inline int g_tune_wide_nt = 128;
+inline int g_tune_min_k_iters = 8;  // k-iterations (of 32) a split must keep; fewer, fatter splits = less workspace traffic
 
 inline int pick_splits(int tiles, int k_iters, int nt, int forced) {
   int splits = 1;
@@ -107,7 +124,7 @@ inline int pick_splits(int tiles, int k_iters, int nt, int forced) {
     splits = forced;
   } else if (tiles < g_tune_target_ctas) {
     splits = g_tune_target_ctas / tiles;
-    int max_by_k = k_iters / 4;  // keep >= 4 k-iterations (128 of K) per split
+    int max_by_k = k_iters / g_tune_min_k_iters;  // keep a minimum amount of K per split
     if (max_by_k < 1) max_by_k = 1;
     if (splits > max_by_k) splits = max_by_k;
   }
@@ -170,7 +187,8 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
       if ((rc = make_map_f32(&mB, w, 2, dims, str, box, true))) return rc;
     }
     grid = dim3(m_tiles, n_tiles, p.splits);
-    if (out_m_tiles) *out_m_tiles = p.splits > 1 ? 4 * m_tiles : m_tiles;  // BatchNorm partial rows written
+    if (out_m_tiles)  // BatchNorm partial rows written
+      *out_m_tiles = p.splits > 1 ? splitk_pieces(m_tiles * n_tiles, m_tiles, nt) * m_tiles : m_tiles;
     if (mode == kFprop) return launch_conv_gemm_mode<kFprop>(nt, mA, mB, p, grid, stream);
     return launch_conv_gemm_mode<kDgrad>(nt, mA, mB, p, grid, stream);
   }

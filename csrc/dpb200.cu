@@ -52,6 +52,8 @@ int dpb_set_tuning(int key, int value) {
   if (key == 0 && value >= 1) { g_tune_target_ctas = value; return 0; }
   if (key == 1 && (value == 64 || value == 128 || value == 256)) { g_tune_wide_nt = value; return 0; }
   if (key == 2 && value >= 1 && value <= kCommMaxBlocks) { g_tune_comm_blocks = value; return 0; }
+  if (key == 3 && value >= 1) { g_tune_min_k_iters = value; return 0; }
+  if (key == 4) { g_tune_use_pdl = value ? 1 : 0; return 0; }
   return set_error(-30, "dpb_set_tuning: bad key/value %d/%d", key, value);
 }
 
@@ -85,8 +87,7 @@ int dpb_first_conv_fprop(const float* x, const float* weight, const float* bias,
                          float* part_sq, int n, int h, int w, dpb_stream_t stream) {
   if (int rc = first_conv_check(w)) return rc;
   const int blocks = dpb_first_conv_blocks(n, h, w);
-  first_conv_fprop_kernel<<<blocks, 256, 0, S(stream)>>>(x, weight, bias, y, part_sum, part_sq, n, h, w);
-  DPB_CUDA(cudaGetLastError());
+  DPB_CUDA(launch_k(first_conv_fprop_kernel, dim3(blocks), dim3(256), 0, S(stream), x, weight, bias, y, part_sum, part_sq, n, h, w));
   return 0;
 }
 
@@ -97,11 +98,9 @@ int dpb_first_conv_wgrad(const float* x, const float* dy, float* partials, float
   if (int rc = first_conv_check(w)) return rc;
   int blocks = dpb_first_conv_blocks(n, h, w);
   if (blocks > kFirstWgradBlocks) blocks = kFirstWgradBlocks;
-  first_conv_wgrad_kernel<<<blocks, 256, 0, S(stream)>>>(x, dy, partials, n, h, w);
-  DPB_CUDA(cudaGetLastError());
+  DPB_CUDA(launch_k(first_conv_wgrad_kernel, dim3(blocks), dim3(256), 0, S(stream), x, dy, partials, n, h, w));
   const int nout = 64 * 27;
-  column_reduce_kernel<<<(nout + 31) / 32, dim3(32, 8), 0, S(stream)>>>(partials, blocks, nout, dw);
-  DPB_CUDA(cudaGetLastError());
+  DPB_CUDA(launch_k(column_reduce_kernel, dim3((nout + 31) / 32), dim3(32, 8), 0, S(stream), partials, blocks, nout, dw));
   return 0;
 }
 
@@ -110,18 +109,13 @@ int dpb_bn_finalize(const float* part_sum, const float* part_sq, int parts, int 
                     const float* beta, float* running_mean, float* running_var, long long* nbt, float momentum,
                     float eps, float* scale, float* shift, float* save_mean, float* save_invstd,
                     dpb_stream_t stream) {
-  bn_finalize_kernel<<<(c + 31) / 32, dim3(32, 32), 0, S(stream)>>>(part_sum, part_sq, parts, c, count, gamma, beta,
-                                                                   running_mean, running_var, nbt, momentum, eps,
-                                                                   scale, shift, save_mean, save_invstd);
-  DPB_CUDA(cudaGetLastError());
+  DPB_CUDA(launch_k(bn_finalize_kernel, dim3((c + 31) / 32), dim3(32, 32), 0, S(stream), part_sum, part_sq, parts, c, count, gamma, beta, running_mean, running_var, nbt, momentum, eps, scale, shift, save_mean, save_invstd));
   return 0;
 }
 
 int dpb_bn_eval_scale_shift(int c, const float* gamma, const float* beta, const float* running_mean,
                             const float* running_var, float eps, float* scale, float* shift, dpb_stream_t stream) {
-  bn_eval_scale_shift_kernel<<<(c + 127) / 128, 128, 0, S(stream)>>>(c, gamma, beta, running_mean, running_var, eps,
-                                                                    scale, shift);
-  DPB_CUDA(cudaGetLastError());
+  DPB_CUDA(launch_k(bn_eval_scale_shift_kernel, dim3((c + 127) / 128), dim3(128), 0, S(stream), c, gamma, beta, running_mean, running_var, eps, scale, shift));
   return 0;
 }
 
@@ -132,11 +126,11 @@ int dpb_bn_relu_pool_fwd(const float* y, const float* scale, const float* shift,
   const long long opix = pool ? (long long)n * (h / 2) * (w / 2) : (long long)n * h * w;
   const long long units = opix * (c / 4);
   const int blocks = grid_for(units, 256, 148 * 16);
-  if (pool)
-    bn_relu_pool_fwd_kernel<true><<<blocks, 256, 0, S(stream)>>>(y, scale, shift, out, units, c / 4, h, w);
-  else
-    bn_relu_pool_fwd_kernel<false><<<blocks, 256, 0, S(stream)>>>(y, scale, shift, out, units, c / 4, h, w);
-  DPB_CUDA(cudaGetLastError());
+  if (pool) {
+    DPB_CUDA(launch_k(bn_relu_pool_fwd_kernel<true>, dim3(blocks), dim3(256), 0, S(stream), y, scale, shift, out, units, c / 4, h, w));
+  } else {
+    DPB_CUDA(launch_k(bn_relu_pool_fwd_kernel<false>, dim3(blocks), dim3(256), 0, S(stream), y, scale, shift, out, units, c / 4, h, w));
+  }
   return 0;
 }
 
@@ -155,25 +149,20 @@ int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, 
   float* part_g = part;
   float* part_gx = part + (size_t)kBnBwdBlocks * c;
   const size_t smem = 2 * 256 * sizeof(float4);
-  if (pool)
-    bn_bwd_reduce_kernel<true><<<blocks, 256, smem, S(stream)>>>(y, dout, scale, shift, save_mean, save_invstd,
-                                                                 part_g, part_gx, opix, c4, h, w);
-  else
-    bn_bwd_reduce_kernel<false><<<blocks, 256, smem, S(stream)>>>(y, dout, scale, shift, save_mean, save_invstd,
-                                                                  part_g, part_gx, opix, c4, h, w);
-  DPB_CUDA(cudaGetLastError());
+  if (pool) {
+    DPB_CUDA(launch_k(bn_bwd_reduce_kernel<true>, dim3(blocks), dim3(256), smem, S(stream), y, dout, scale, shift, save_mean, save_invstd, part_g, part_gx, opix, c4, h, w));
+  } else {
+    DPB_CUDA(launch_k(bn_bwd_reduce_kernel<false>, dim3(blocks), dim3(256), smem, S(stream), y, dout, scale, shift, save_mean, save_invstd, part_g, part_gx, opix, c4, h, w));
+  }
   const double count = (double)n * h * w;
-  bn_bwd_finalize_kernel<<<(c + 31) / 32, dim3(32, 32), 0, S(stream)>>>(part_g, part_gx, blocks, c, count, gamma,
-                                                                       save_mean, save_invstd, dgamma, dbeta, conv_dbias,
-                                                                       coef);
-  DPB_CUDA(cudaGetLastError());
+  DPB_CUDA(launch_k(bn_bwd_finalize_kernel, dim3((c + 31) / 32), dim3(32, 32), 0, S(stream), part_g, part_gx, blocks, c, count, gamma, save_mean, save_invstd, dgamma, dbeta, conv_dbias, coef));
   const long long units = opix * c4;
   const int ablocks = grid_for(units, 256, 148 * 16);
-  if (pool)
-    bn_bwd_apply_kernel<true><<<ablocks, 256, 0, S(stream)>>>(y, dout, scale, shift, coef, dy, units, c, h, w);
-  else
-    bn_bwd_apply_kernel<false><<<ablocks, 256, 0, S(stream)>>>(y, dout, scale, shift, coef, dy, units, c, h, w);
-  DPB_CUDA(cudaGetLastError());
+  if (pool) {
+    DPB_CUDA(launch_k(bn_bwd_apply_kernel<true>, dim3(ablocks), dim3(256), 0, S(stream), y, dout, scale, shift, coef, dy, units, c, h, w));
+  } else {
+    DPB_CUDA(launch_k(bn_bwd_apply_kernel<false>, dim3(ablocks), dim3(256), 0, S(stream), y, dout, scale, shift, coef, dy, units, c, h, w));
+  }
   return 0;
 }
 
@@ -181,8 +170,7 @@ int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, 
 int dpb_linear_fwd(const float* x, const float* w, const float* bias, float* out, int b, int k, int o,
                    dpb_stream_t stream) {
   if (o > kMaxClasses) return set_error(-3, "linear: out_features %d > %d", o, kMaxClasses);
-  linear_fwd_kernel<<<(b * 32 + 127) / 128, 128, 0, S(stream)>>>(x, w, bias, out, b, k, o);
-  DPB_CUDA(cudaGetLastError());
+  DPB_CUDA(launch_k(linear_fwd_kernel, dim3((b * 32 + 127) / 128), dim3(128), 0, S(stream), x, w, bias, out, b, k, o));
   return 0;
 }
 
@@ -191,27 +179,23 @@ int dpb_linear_bwd(const float* dz, const float* x, const float* w, float* dx, f
   if (o > kMaxClasses) return set_error(-3, "linear: out_features %d > %d", o, kMaxClasses);
   if (dx != nullptr) {
     const long long n = (long long)b * k;
-    linear_bwd_input_kernel<<<(int)((n + 255) / 256), 256, 0, S(stream)>>>(dz, w, dx, b, k, o);
-    DPB_CUDA(cudaGetLastError());
+    DPB_CUDA(launch_k(linear_bwd_input_kernel, dim3((int)((n + 255) / 256)), dim3(256), 0, S(stream), dz, w, dx, b, k, o));
   }
   if (dw != nullptr) {
-    linear_bwd_weight_kernel<<<(k + 31) / 32, dim3(32, 8), 0, S(stream)>>>(dz, x, dw, db, b, k, o);
-    DPB_CUDA(cudaGetLastError());
+    DPB_CUDA(launch_k(linear_bwd_weight_kernel, dim3((k + 31) / 32), dim3(32, 8), 0, S(stream), dz, x, dw, db, b, k, o));
   }
   return 0;
 }
 
 int dpb_cross_entropy_fwd(const float* logits, const long long* target, float* loss, float* metrics, int b, int o,
                           dpb_stream_t stream) {
-  cross_entropy_fwd_kernel<<<1, 256, 0, S(stream)>>>(logits, target, loss, metrics, b, o);
-  DPB_CUDA(cudaGetLastError());
+  DPB_CUDA(launch_k(cross_entropy_fwd_kernel, dim3(1), dim3(256), 0, S(stream), logits, target, loss, metrics, b, o));
   return 0;
 }
 
 int dpb_cross_entropy_bwd(const float* logits, const long long* target, const float* grad_out, float* dz, int b,
                           int o, dpb_stream_t stream) {
-  cross_entropy_bwd_kernel<<<(b + 255) / 256, 256, 0, S(stream)>>>(logits, target, grad_out, dz, b, o);
-  DPB_CUDA(cudaGetLastError());
+  DPB_CUDA(launch_k(cross_entropy_bwd_kernel, dim3((b + 255) / 256), dim3(256), 0, S(stream), logits, target, grad_out, dz, b, o));
   return 0;
 }
 
@@ -223,16 +207,12 @@ int dpb_sgd_step(float* p, const float* g, float* m, long long n, float lr, floa
                          reinterpret_cast<uintptr_t>(m)) & 15) == 0;
   long long n4 = aligned ? n / 4 : 0;
   if (n4 > 0) {
-    sgd_kernel<<<grid_for(n4, 256, 148 * 8), 256, 0, S(stream)>>>(p, g, m, n4, lr, momentum, wd, grad_scale,
-                                                                  nesterov);
-    DPB_CUDA(cudaGetLastError());
+    DPB_CUDA(launch_k(sgd_kernel, dim3(grid_for(n4, 256, 148 * 8)), dim3(256), 0, S(stream), p, g, m, n4, lr, momentum, wd, grad_scale, nesterov));
   }
   const long long rem = n - n4 * 4;
   if (rem > 0) {
     const long long o = n4 * 4;
-    sgd_scalar_kernel<<<(int)((rem + 255) / 256), 256, 0, S(stream)>>>(p + o, g + o, m ? m + o : nullptr, rem, lr,
-                                                                       momentum, wd, grad_scale, nesterov);
-    DPB_CUDA(cudaGetLastError());
+    DPB_CUDA(launch_k(sgd_scalar_kernel, dim3((int)((rem + 255) / 256)), dim3(256), 0, S(stream), p + o, g + o, m ? m + o : nullptr, rem, lr, momentum, wd, grad_scale, nesterov));
   }
   return 0;
 }

@@ -60,6 +60,7 @@ __global__ void __launch_bounds__(256, 1)
 first_conv_fprop_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                         float* __restrict__ y, float* __restrict__ part_sum, float* __restrict__ part_sq, int N, int H,
                         int W) {
+  pdl_prologue();
   __shared__ float xs[2][FcTile::kMaxElems];
   __shared__ float red[8][2][64];
   const int cg = threadIdx.x & 15;  // output channels 4cg .. 4cg+3
@@ -171,6 +172,7 @@ first_conv_fprop_kernel(const float* __restrict__ x, const float* __restrict__ w
 __global__ void __launch_bounds__(256, 1)
 first_conv_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ partials, int N,
                         int H, int W) {
+  pdl_prologue();
   __shared__ float xs[2][FcTile::kMaxElems];
   __shared__ float red[4][64 * 27];  // 27.6 KB
   const int cg = threadIdx.x & 15;   // output channels 4cg .. 4cg+3
@@ -286,6 +288,7 @@ first_conv_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ d
 
 // out[c] = sum_t partials[t][c], fixed order.  grid = ceil(n/32) blocks of (32, 8).
 __global__ void column_reduce_kernel(const float* __restrict__ partials, int T, int n, float* __restrict__ out) {
+  pdl_prologue();
   __shared__ float s[8][33];
   const int cx = threadIdx.x, ry = threadIdx.y;
   const int c = blockIdx.x * 32 + cx;

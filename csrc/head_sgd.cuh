@@ -20,6 +20,7 @@ __device__ __forceinline__ float warp_sum(float v) {
 __global__ void __launch_bounds__(128)
 linear_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                   float* __restrict__ out, int B, int K, int O) {
+  pdl_prologue();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= B) return;
@@ -62,6 +63,7 @@ linear_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, cons
 __global__ void __launch_bounds__(256)
 linear_bwd_input_kernel(const float* __restrict__ dz, const float* __restrict__ w, float* __restrict__ dx, int B, int K,
                         int O) {
+  pdl_prologue();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long long)B * K) return;
   const int b = (int)(i / K), k = (int)(i - (long long)b * K);
@@ -76,6 +78,7 @@ linear_bwd_input_kernel(const float* __restrict__ dz, const float* __restrict__ 
 // by the 8 row lanes and combined in a fixed order.  Block 0 also produces db.
 __global__ void linear_bwd_weight_kernel(const float* __restrict__ dz, const float* __restrict__ x,
                                          float* __restrict__ dw, float* __restrict__ db, int B, int K, int O) {
+  pdl_prologue();
   __shared__ float s[8][kMaxClasses][33];
   const int cx = threadIdx.x, ry = threadIdx.y;
   const int k = blockIdx.x * 32 + cx;
@@ -131,6 +134,7 @@ __global__ void linear_bwd_weight_kernel(const float* __restrict__ dz, const flo
 __global__ void __launch_bounds__(256)
 cross_entropy_fwd_kernel(const float* __restrict__ logits, const long long* __restrict__ target,
                          float* __restrict__ loss_out, float* __restrict__ metrics, int B, int O) {
+  pdl_prologue();
   __shared__ float s_loss[8], s_hit[8];
   float lsum = 0.f, hits = 0.f;
   for (int b = threadIdx.x; b < B; b += 256) {
@@ -163,6 +167,7 @@ cross_entropy_fwd_kernel(const float* __restrict__ logits, const long long* __re
 __global__ void __launch_bounds__(256)
 cross_entropy_bwd_kernel(const float* __restrict__ logits, const long long* __restrict__ target,
                          const float* __restrict__ grad_out, float* __restrict__ dz, int B, int O) {
+  pdl_prologue();
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   const float gs = (grad_out ? grad_out[0] : 1.f) / (float)B;
@@ -182,6 +187,7 @@ cross_entropy_bwd_kernel(const float* __restrict__ logits, const long long* __re
 __global__ void __launch_bounds__(256)
 sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, long long n4, float lr,
            float momentum, float wd, float grad_scale, int nesterov) {
+  pdl_prologue();
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 pv = reinterpret_cast<float4*>(p)[i];
@@ -208,6 +214,7 @@ sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict
 // scalar tail / unaligned fallback
 __global__ void sgd_scalar_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                   long long n, float lr, float momentum, float wd, float grad_scale, int nesterov) {
+  pdl_prologue();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float ge = fmaf(wd, p[i], g[i] * grad_scale);

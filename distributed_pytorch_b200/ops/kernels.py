@@ -69,7 +69,8 @@ def conv3x3_gemm(mode: int, n: int, h: int, w: int, cin: int, cout: int, inp: to
     stat_sum = stat_sq = None
     m_tiles = ctypes.c_int(0)
     if want_stats:
-        tiles = 4 * ((n * h * w + 127) // 128)  # split-K leaves 4 partial rows per 128-pixel tile, else 1
+        tiles = (n * h * w + 127) // 128
+        tiles *= 32 if tiles <= 64 else 4  # split-K leaves up to 32 (<= 64 tiles) / 4 partial rows per tile, else 1
         stat_sum = torch.empty((tiles, cout), device=out.device, dtype=torch.float32)
         stat_sq = torch.empty((tiles, cout), device=out.device, dtype=torch.float32)
     N.check(lib.dpb_conv3x3_gemm(mode, n, h, w, cin, cout, N.ptr(inp), N.ptr(inp2), N.ptr(weight), N.ptr(out),
