@@ -57,13 +57,21 @@ struct ConvGemmSmem {
   static constexpr int kTotal = 1024 /*align slack*/ + STAGES * kStageBytes + kBarBytes + 2 * NT * 4 * 4;
 };
 
-template <int MODE, int NT, int STAGES>
+// CL > 1: thread-block cluster of CL CTAs along blockIdx.x (neighbouring M tiles, same N tile / tap / split).  They
+// consume the same B tile, so each CTA fetches 1/CL of it and TMA-multicasts it into every CTA's shared memory: B's
+// L2 -> SM traffic drops by CL.  A stage may be refilled only when all CL CTAs have consumed it, hence the empty
+// barriers count CL arrivals and every MMA commit is multicast to the whole cluster.
+template <int MODE, int NT, int STAGES, int CL>
 __global__ void __launch_bounds__(192, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                  const ConvGemmParams p) {
   constexpr bool A_MN = (MODE == kWgrad);
   constexpr bool B_MN = (MODE != kFprop);
   using S = ConvGemmSmem<NT, STAGES>;
+  static_assert(CL == 1 || CL == 2 || CL == 4, "cluster size");
+  static_assert((NT / 32) % CL == 0, "B tile must split evenly over the cluster");
+  constexpr uint16_t kClusterMask = (uint16_t)((1u << CL) - 1u);
+  const uint32_t crank = (CL > 1) ? cluster_ctarank() : 0u;
 
   pdl_launch_dependents();  // the next kernel may start its prologue; it waits for our completion itself
   extern __shared__ uint8_t smem_raw[];
@@ -97,14 +105,15 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 #pragma unroll
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
+      mbar_init(&empty_bar[s], CL);  // one arrival per CTA of the cluster (each CTA's MMA commit is multicast)
     }
     mbar_init(acc_bar, 1);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc<NT>(tmem_slot);
   tc_fence_before();
-  __syncthreads();
+  if (CL > 1) cluster_sync_all();  // peers must see initialised barriers before any multicast lands
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_acc = *tmem_slot;
 
@@ -135,15 +144,29 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           const int tap = kk / cpt, cc = kk - tap * cpt;
           const int r = tap / 3, sx = tap - 3 * r;
           tma_load_4d(sa, &mapA, &full_bar[s], cc * 32, a_w0 + sx - 1, a_h0 + r - 1, a_n0);
-          tma_load_2d(sb, &mapB, &full_bar[s], tap * p.CinW + cc * 32, n_tile * NT);
+          if (CL == 1) {
+            tma_load_2d(sb, &mapB, &full_bar[s], tap * p.CinW + cc * 32, n_tile * NT);
+          } else {  // my NT/CL weight rows, delivered to every CTA of the cluster (mapB's box is NT/CL rows)
+            tma_load_2d_mc(sb + crank * (NT / CL) * 128, &mapB, &full_bar[s], tap * p.CinW + cc * 32,
+                           n_tile * NT + crank * (NT / CL), kClusterMask);
+          }
         } else if (MODE == kDgrad) {
           const int tap = kk / cpt, cc = kk - tap * cpt;
           const int r = tap / 3, sx = tap - 3 * r;
           tma_load_4d(sa, &mapA, &full_bar[s], cc * 32, a_w0 + sx - 1, a_h0 + r - 1, a_n0);
           // MN-major B: one 32(co = GEMM K) x 32(ci = GEMM N) box of the KRSC weights per 32-wide N atom, flipped tap
+          if (CL == 1) {
 #pragma unroll
-          for (int a = 0; a < NT / 32; ++a)
-            tma_load_2d(sb + a * 4096, &mapB, &full_bar[s], (8 - tap) * p.CinW + n_tile * NT + a * 32, cc * 32);
+            for (int a = 0; a < NT / 32; ++a)
+              tma_load_2d(sb + a * 4096, &mapB, &full_bar[s], (8 - tap) * p.CinW + n_tile * NT + a * 32, cc * 32);
+          } else {
+#pragma unroll
+            for (int j = 0; j < NT / 32 / CL; ++j) {
+              const int a = crank * (NT / 32 / CL) + j;
+              tma_load_2d_mc(sb + a * 4096, &mapB, &full_bar[s], (8 - tap) * p.CinW + n_tile * NT + a * 32, cc * 32,
+                             kClusterMask);
+            }
+          }
         } else {
           const int r = wtap / 3, sx = wtap - 3 * r;
           const int p0 = kk * 32;
@@ -154,9 +177,18 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 #pragma unroll
           for (int a = 0; a < 4; ++a)
             tma_load_2d(sa + a * 4096, &mapA, &full_bar[s], m_tile * 128 + a * 32, p0);
+          if (CL == 1) {
 #pragma unroll
-          for (int a = 0; a < NT / 32; ++a)
-            tma_load_4d(sb + a * 4096, &mapB, &full_bar[s], n_tile * NT + a * 32, w0 + sx - 1, h0 + r - 1, n0);
+            for (int a = 0; a < NT / 32; ++a)
+              tma_load_4d(sb + a * 4096, &mapB, &full_bar[s], n_tile * NT + a * 32, w0 + sx - 1, h0 + r - 1, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < NT / 32 / CL; ++j) {
+              const int a = crank * (NT / 32 / CL) + j;
+              tma_load_4d_mc(sb + a * 4096, &mapB, &full_bar[s], n_tile * NT + a * 32, w0 + sx - 1, h0 + r - 1, n0,
+                             kClusterMask);
+            }
+          }
         }
       }
     }
@@ -189,7 +221,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           const uint64_t bd = umma_smem_desc(sb + ks * b_kstep, b_lbo, b_sbo, b_lt);
           umma_tf32(tmem_acc, ad, bd, idesc, (i > 0 || ks > 0) ? 1u : 0u);
         }
-        umma_commit(&empty_bar[s]);              // frees the smem slot when these MMAs retire
+        // frees the smem slot when these MMAs retire (in every CTA of the cluster: peers write our B slice too)
+        if (CL == 1) umma_commit(&empty_bar[s]);
+        else umma_commit_mc(&empty_bar[s], kClusterMask);
         if (i == k_count - 1) umma_commit(acc_bar);  // accumulator complete
       }
       __syncwarp();
@@ -271,8 +305,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     // split-K: the partial tile is in the workspace; splitk_reduce_kernel (next launch) finishes the job
   }
 
+  __syncwarp();  // re-converge the single-lane producer / issuer warps before the aligned barrier
   tc_fence_before();
-  __syncthreads();
+  // a CTA must not retire while a peer's commit can still arrive on its barriers
+  if (CL > 1) cluster_sync_all();
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc<NT>(tmem_acc);

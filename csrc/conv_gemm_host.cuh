@@ -76,18 +76,34 @@ inline void pixel_box(int h, int w, int pixels, int* bw, int* bh, int* bn) {
   *bn = rest / *bh;
 }
 
-template <int MODE, int NT>
-int launch_conv_gemm_nt(const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
+template <int MODE, int NT, int CL>
+int launch_conv_gemm_cl(const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
                         cudaStream_t stream) {
   constexpr int STAGES = (NT == 128) ? 3 : 4;  // NT 64: 4 x 24 KB, NT 128: 3 x 32 KB (two CTAs per SM); NT 256: 4 x 48 KB
   using S = ConvGemmSmem<NT, STAGES>;
-  auto kern = conv_gemm_kernel<MODE, NT, STAGES>;
+  auto kern = conv_gemm_kernel<MODE, NT, STAGES, CL>;
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     DPB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
     attr_set = true;
   }
-  DPB_CUDA(launch_k(kern, grid, dim3(192), S::kTotal, stream, mA, mB, p));
+  if (CL == 1) {
+    DPB_CUDA(launch_k(kern, grid, dim3(192), S::kTotal, stream, mA, mB, p));
+  } else {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(192);
+    cfg.dynamicSmemBytes = S::kTotal;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CL;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    DPB_CUDA(cudaLaunchKernelEx(&cfg, kern, mA, mB, p));
+  }
   g_conv_last_launches = p.splits > 1 ? 2 : 1;
   if (p.splits > 1) {
     const int m_tiles = grid.x, n_tiles = grid.y;
@@ -98,15 +114,33 @@ int launch_conv_gemm_nt(const CUtensorMap& mA, const CUtensorMap& mB, const Conv
   return 0;
 }
 
+template <int MODE, int NT>
+int launch_conv_gemm_nt(int cl, const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
+                        cudaStream_t stream) {
+  if (cl == 2) return launch_conv_gemm_cl<MODE, NT, 2>(mA, mB, p, grid, stream);
+  if constexpr (NT >= 128) {
+    if (cl == 4) return launch_conv_gemm_cl<MODE, NT, 4>(mA, mB, p, grid, stream);
+  }
+  return launch_conv_gemm_cl<MODE, NT, 1>(mA, mB, p, grid, stream);
+}
+
 template <int MODE>
-int launch_conv_gemm_mode(int nt, const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
-                          cudaStream_t stream) {
+int launch_conv_gemm_mode(int nt, int cl, const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p,
+                          dim3 grid, cudaStream_t stream) {
   switch (nt) {
-    case 64: return launch_conv_gemm_nt<MODE, 64>(mA, mB, p, grid, stream);
-    case 128: return launch_conv_gemm_nt<MODE, 128>(mA, mB, p, grid, stream);
-    case 256: return launch_conv_gemm_nt<MODE, 256>(mA, mB, p, grid, stream);
+    case 64: return launch_conv_gemm_nt<MODE, 64>(cl, mA, mB, p, grid, stream);
+    case 128: return launch_conv_gemm_nt<MODE, 128>(cl, mA, mB, p, grid, stream);
+    case 256: return launch_conv_gemm_nt<MODE, 256>(cl, mA, mB, p, grid, stream);
   }
   return set_error(-12, "unsupported N tile %d", nt);
+}
+
+// Cluster size along M for B-tile multicast: the largest of {tuned value, 2, 1} that divides the M tiles and the B atoms.
+inline int g_tune_cluster = 1;
+inline int pick_cluster(int m_tiles, int nt) {
+  int cl = g_tune_cluster;
+  while (cl > 1 && (m_tiles % cl != 0 || (nt / 32) % cl != 0)) cl >>= 1;
+  return cl < 1 ? 1 : cl;
 }
 
 constexpr size_t kConvWorkspaceBytes = (size_t)48 << 20;  // split-K partial tiles
@@ -169,6 +203,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
     const int m_tiles = (int)((pixels + 127) / 128);
     const int n_tiles = cn / nt;
     p.splits = pick_splits(m_tiles * n_tiles, p.k_iters, nt, splits_override);
+    const int cl = pick_cluster(m_tiles, nt);
     {
       cuuint64_t dims[4] = {(cuuint64_t)ck, (cuuint64_t)g.w, (cuuint64_t)g.h, (cuuint64_t)g.n};
       cuuint64_t str[3] = {(cuuint64_t)ck * 4, (cuuint64_t)g.w * ck * 4, (cuuint64_t)g.h * g.w * ck * 4};
@@ -178,7 +213,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
     if (mode == kFprop) {
       cuuint64_t dims[2] = {(cuuint64_t)9 * g.cin, (cuuint64_t)g.cout};
       cuuint64_t str[1] = {(cuuint64_t)9 * g.cin * 4};
-      cuuint32_t box[2] = {32, (cuuint32_t)nt};
+      cuuint32_t box[2] = {32, (cuuint32_t)(nt / cl)};  // each CTA of a cluster fetches (and multicasts) nt/cl rows
       if ((rc = make_map_f32(&mB, w, 2, dims, str, box))) return rc;
     } else {
       cuuint64_t dims[2] = {(cuuint64_t)9 * g.cin, (cuuint64_t)g.cout};
@@ -189,8 +224,8 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
     grid = dim3(m_tiles, n_tiles, p.splits);
     if (out_m_tiles)  // BatchNorm partial rows written
       *out_m_tiles = p.splits > 1 ? splitk_pieces(m_tiles * n_tiles, m_tiles, nt) * m_tiles : m_tiles;
-    if (mode == kFprop) return launch_conv_gemm_mode<kFprop>(nt, mA, mB, p, grid, stream);
-    return launch_conv_gemm_mode<kDgrad>(nt, mA, mB, p, grid, stream);
+    if (mode == kFprop) return launch_conv_gemm_mode<kFprop>(nt, cl, mA, mB, p, grid, stream);
+    return launch_conv_gemm_mode<kDgrad>(nt, cl, mA, mB, p, grid, stream);
   }
   // wgrad
   nt = nt_override > 0 ? nt_override : (g.cin % g_tune_wide_nt == 0 ? g_tune_wide_nt : (g.cin >= 128 ? 128 : 64));
@@ -219,7 +254,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
   }
   grid = dim3(m_tiles, n_tiles, 9 * p.splits);
   if (out_m_tiles) *out_m_tiles = m_tiles;
-  return launch_conv_gemm_mode<kWgrad>(nt, mA, mB, p, grid, stream);
+  return launch_conv_gemm_mode<kWgrad>(nt, pick_cluster(m_tiles, nt), mA, mB, p, grid, stream);
 }
 
 }  // namespace dpb

@@ -54,6 +54,7 @@ int dpb_set_tuning(int key, int value) {
   if (key == 2 && value >= 1 && value <= kCommMaxBlocks) { g_tune_comm_blocks = value; return 0; }
   if (key == 3 && value >= 1) { g_tune_min_k_iters = value; return 0; }
   if (key == 4) { g_tune_use_pdl = value ? 1 : 0; return 0; }
+  if (key == 5 && (value == 1 || value == 2 || value == 4)) { g_tune_cluster = value; return 0; }
   return set_error(-30, "dpb_set_tuning: bad key/value %d/%d", key, value);
 }
 
