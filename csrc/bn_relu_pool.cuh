@@ -13,8 +13,13 @@
 
 namespace dpb {
 
+// Finalize kernels: block = (kFinCh channels, kFinRows row lanes), grid = C / kFinCh.  Few channels per block keeps
+// the per-thread chain over the partial rows short (T / 128 loads): these kernels are pure latency.
+constexpr int kFinCh = 8;
+constexpr int kFinRows = 128;
+
 // ------------------------------------------------------------------------------------------------ forward finalize
-// grid = C/32 blocks of (32, 32) threads.  Partials are combined in double, in a fixed order.
+// Partials are combined in double, in a fixed order.
 __global__ void bn_finalize_kernel(const float* __restrict__ part_sum, const float* __restrict__ part_sq, int T, int C,
                                    double count, const float* __restrict__ gamma, const float* __restrict__ beta,
                                    float* __restrict__ running_mean, float* __restrict__ running_var,
@@ -22,13 +27,13 @@ __global__ void bn_finalize_kernel(const float* __restrict__ part_sum, const flo
                                    float* __restrict__ scale, float* __restrict__ shift, float* __restrict__ save_mean,
                                    float* __restrict__ save_invstd) {
   pdl_prologue();
-  __shared__ double s_sum[32][33], s_sq[32][33];
+  __shared__ double s_sum[kFinRows][kFinCh + 1], s_sq[kFinRows][kFinCh + 1];
   const int cx = threadIdx.x, ry = threadIdx.y;
-  const int c = blockIdx.x * 32 + cx;
+  const int c = blockIdx.x * kFinCh + cx;
   double a = 0.0, b = 0.0;
   if (c < C) {
 #pragma unroll 4
-    for (int t = ry; t < T; t += 32) {
+    for (int t = ry; t < T; t += kFinRows) {
       a += (double)part_sum[(size_t)t * C + c];
       b += (double)part_sq[(size_t)t * C + c];
     }
@@ -36,10 +41,22 @@ __global__ void bn_finalize_kernel(const float* __restrict__ part_sum, const flo
   s_sum[ry][cx] = a;
   s_sq[ry][cx] = b;
   __syncthreads();
+  if (ry < 8) {  // 128 -> 8 row lanes, fixed order
+    double u = 0.0, v = 0.0;
+#pragma unroll
+    for (int r = ry; r < kFinRows; r += 8) {
+      u += s_sum[r][cx];
+      v += s_sq[r][cx];
+    }
+    __syncwarp();
+    s_sum[ry][cx] = u;
+    s_sq[ry][cx] = v;
+  }
+  __syncthreads();
   if (ry == 0 && c < C) {
     double sum = 0.0, sq = 0.0;
 #pragma unroll
-    for (int r = 0; r < 32; ++r) {
+    for (int r = 0; r < 8; ++r) {
       sum += s_sum[r][cx];
       sq += s_sq[r][cx];
     }
@@ -222,13 +239,13 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ part_g, const f
                                        float* __restrict__ dgamma, float* __restrict__ dbeta,
                                        float* __restrict__ conv_dbias, float* __restrict__ coef /* [3][C] */) {
   pdl_prologue();
-  __shared__ double s_a[32][33], s_b[32][33];
+  __shared__ double s_a[kFinRows][kFinCh + 1], s_b[kFinRows][kFinCh + 1];
   const int cx = threadIdx.x, ry = threadIdx.y;
-  const int c = blockIdx.x * 32 + cx;
+  const int c = blockIdx.x * kFinCh + cx;
   double a = 0.0, b = 0.0;
   if (c < C) {
 #pragma unroll 4
-    for (int t = ry; t < T; t += 32) {
+    for (int t = ry; t < T; t += kFinRows) {
       a += (double)part_g[(size_t)t * C + c];
       b += (double)part_gx[(size_t)t * C + c];
     }
@@ -236,10 +253,22 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ part_g, const f
   s_a[ry][cx] = a;
   s_b[ry][cx] = b;
   __syncthreads();
+  if (ry < 8) {  // 128 -> 8 row lanes, fixed order
+    double u = 0.0, v = 0.0;
+#pragma unroll
+    for (int r = ry; r < kFinRows; r += 8) {
+      u += s_a[r][cx];
+      v += s_b[r][cx];
+    }
+    __syncwarp();
+    s_a[ry][cx] = u;
+    s_b[ry][cx] = v;
+  }
+  __syncthreads();
   if (ry == 0 && c < C) {
     double sg = 0.0, sgx = 0.0;
 #pragma unroll
-    for (int r = 0; r < 32; ++r) {
+    for (int r = 0; r < 8; ++r) {
       sg += s_a[r][cx];
       sgx += s_b[r][cx];
     }

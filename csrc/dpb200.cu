@@ -110,7 +110,7 @@ int dpb_bn_finalize(const float* part_sum, const float* part_sq, int parts, int 
                     const float* beta, float* running_mean, float* running_var, long long* nbt, float momentum,
                     float eps, float* scale, float* shift, float* save_mean, float* save_invstd,
                     dpb_stream_t stream) {
-  DPB_CUDA(launch_k(bn_finalize_kernel, dim3((c + 31) / 32), dim3(32, 32), 0, S(stream), part_sum, part_sq, parts, c, count, gamma, beta, running_mean, running_var, nbt, momentum, eps, scale, shift, save_mean, save_invstd));
+  DPB_CUDA(launch_k(bn_finalize_kernel, dim3((c + kFinCh - 1) / kFinCh), dim3(kFinCh, kFinRows), 0, S(stream), part_sum, part_sq, parts, c, count, gamma, beta, running_mean, running_var, nbt, momentum, eps, scale, shift, save_mean, save_invstd));
   return 0;
 }
 
@@ -156,7 +156,7 @@ int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, 
     DPB_CUDA(launch_k(bn_bwd_reduce_kernel<false>, dim3(blocks), dim3(256), smem, S(stream), y, dout, scale, shift, save_mean, save_invstd, part_g, part_gx, opix, c4, h, w));
   }
   const double count = (double)n * h * w;
-  DPB_CUDA(launch_k(bn_bwd_finalize_kernel, dim3((c + 31) / 32), dim3(32, 32), 0, S(stream), part_g, part_gx, blocks, c, count, gamma, save_mean, save_invstd, dgamma, dbeta, conv_dbias, coef));
+  DPB_CUDA(launch_k(bn_bwd_finalize_kernel, dim3((c + kFinCh - 1) / kFinCh), dim3(kFinCh, kFinRows), 0, S(stream), part_g, part_gx, blocks, c, count, gamma, save_mean, save_invstd, dgamma, dbeta, conv_dbias, coef));
   const long long units = opix * c4;
   const int ablocks = grid_for(units, 256, 148 * 16);
   if (pool) {
