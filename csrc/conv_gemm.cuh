@@ -42,10 +42,10 @@ struct ConvGemmParams {
   float* debug_dump;       // bring-up aid: CTA (0,0,0) copies its first stage (A then B, as laid out in smem) here
 };
 
-template <int NT, int STAGES>
+template <int NT, int STAGES, int G = 1>
 struct ConvGemmSmem {
   static constexpr int kABytes = 128 * 128;  // 128 rows x 32 tf32
-  static constexpr int kBBytes = NT * 128;
+  static constexpr int kBBytes = NT * 128 / G;  // CTA pair (G = 2): each CTA holds half of the B tile
   static constexpr int kStageBytes = kABytes + kBBytes;
   // The epilogue's per-warp 32x33 fp32 transpose tiles (4 * 32 * 33 * 4 = 16.5 KB) reuse stage 0: by the time the
   // accumulator barrier fires every TMA load has landed and every MMA has finished reading shared memory.  Keeping the
@@ -61,19 +61,39 @@ struct ConvGemmSmem {
 // consume the same B tile, so each CTA fetches 1/CL of it and TMA-multicasts it into every CTA's shared memory: B's
 // L2 -> SM traffic drops by CL.  A stage may be refilled only when all CL CTAs have consumed it, hence the empty
 // barriers count CL arrivals and every MMA commit is multicast to the whole cluster.
-template <int MODE, int NT, int STAGES, int CL>
+//
+// G == 2: CTA pair (tcgen05 cta_group::2).  Two CTAs of a 2-cluster (neighbouring M tiles) run ONE 256 x NT MMA per
+// k-step: each CTA stages its own 128 A rows and only HALF of the B tile, the leader CTA (cluster rank 0) issues the MMA
+// which reads both CTAs' shared memory and writes both CTAs' TMEM.  Per unit of tensor work each SM ingests 25 % (NT
+// 128) to 50 % (NT 256 vs two 128 tiles) fewer operand bytes -- the quantity this kernel is bound by.  Both CTAs' TMA
+// loads credit the leader's full barrier; the leader's commits are multicast to both CTAs' empty / accumulator barriers.
+template <int MODE, int NT, int STAGES, int CL, int G = 1>
 __global__ void __launch_bounds__(192, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                  const ConvGemmParams p) {
   constexpr bool A_MN = (MODE == kWgrad);
   constexpr bool B_MN = (MODE != kFprop);
-  using S = ConvGemmSmem<NT, STAGES>;
+  using S = ConvGemmSmem<NT, STAGES, G>;
   static_assert(CL == 1 || CL == 2 || CL == 4, "cluster size");
-  static_assert((NT / 32) % CL == 0, "B tile must split evenly over the cluster");
+  static_assert(G == 1 || (G == 2 && CL == 1), "CTA pairs do not combine with B multicast");
+  static_assert((NT / 32) % (CL * G) == 0, "B tile must split evenly over the cluster");
   constexpr uint16_t kClusterMask = (uint16_t)((1u << CL) - 1u);
-  const uint32_t crank = (CL > 1) ? cluster_ctarank() : 0u;
+  const uint32_t crank = (CL > 1 || G == 2) ? cluster_ctarank() : 0u;
+  const bool leader = (G == 1) || (crank == 0);
 
   pdl_launch_dependents();  // the next kernel may start its prologue; it waits for our completion itself
+  // bring-up aid: with a debug buffer every CTA logs (globaltimer at entry, at exit, SM id) at word 12800 + 3 * cta
+  const unsigned cta_linear = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+  const bool trace_cta = p.debug_dump != nullptr && cta_linear < 1024u && threadIdx.x == 0;
+  const long long c_entry = clock64();
+  if (trace_cta) {
+    unsigned long long t;
+    unsigned sm;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+    reinterpret_cast<unsigned*>(p.debug_dump)[12800 + 3 * cta_linear] = (unsigned)t;
+    reinterpret_cast<unsigned*>(p.debug_dump)[12800 + 3 * cta_linear + 2] = sm;
+  }
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* stage_base = smem;
@@ -104,15 +124,18 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     tma_prefetch_desc(&mapB);
 #pragma unroll
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&full_bar[s], 1);
+      mbar_init(&full_bar[s], G);    // pair: the leader's barrier collects both CTAs' producer arrivals
       mbar_init(&empty_bar[s], CL);  // one arrival per CTA of the cluster (each CTA's MMA commit is multicast)
     }
     mbar_init(acc_bar, 1);
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc<NT>(tmem_slot);
+  if (warp == 1) {
+    if (G == 2) tmem_alloc_pair<NT>(tmem_slot);
+    else tmem_alloc<NT>(tmem_slot);
+  }
   tc_fence_before();
-  if (CL > 1) cluster_sync_all();  // peers must see initialised barriers before any multicast lands
+  if (CL > 1 || G == 2) cluster_sync_all();  // peers must see initialised barriers before anything remote lands
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_acc = *tmem_slot;
@@ -138,8 +161,41 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         mbar_wait(&empty_bar[s], ph ^ 1, 100 + s);
         uint8_t* sa = stage_base + s * S::kStageBytes;
         uint8_t* sb = sa + S::kABytes;
-        mbar_arrive_expect_tx(&full_bar[s], S::kStageBytes);
         const int kk = k_begin + i;
+        if constexpr (G == 2) {
+          // CTA pair: my A rows and my half of B go to MY shared memory, the bytes are credited to the LEADER's barrier
+          const uint32_t lbar = mapa_u32(&full_bar[s], 0);
+          if (leader) mbar_arrive_expect_tx(&full_bar[s], 2 * S::kStageBytes);
+          else mbar_arrive_cluster(lbar);
+          constexpr int kHalfAtoms = NT / 32 / 2;
+          if (MODE == kFprop || MODE == kDgrad) {
+            const int tap = kk / cpt, cc = kk - tap * cpt;
+            const int r = tap / 3, sx = tap - 3 * r;
+            tma_load_4d_pair(sa, &mapA, lbar, cc * 32, a_w0 + sx - 1, a_h0 + r - 1, a_n0);
+            if (MODE == kFprop) {  // mapB box: NT/2 weight rows
+              tma_load_2d_pair(sb, &mapB, lbar, tap * p.CinW + cc * 32, n_tile * NT + crank * (NT / 2));
+            } else {
+#pragma unroll
+              for (int j = 0; j < kHalfAtoms; ++j)
+                tma_load_2d_pair(sb + j * 4096, &mapB, lbar,
+                                 (8 - tap) * p.CinW + n_tile * NT + (crank * kHalfAtoms + j) * 32, cc * 32);
+            }
+          } else {
+            const int r = wtap / 3, sx = wtap - 3 * r;
+            const int p0 = kk * 32;
+            const int w0 = p0 % p.W;
+            const int h0 = (p0 / p.W) % p.H;
+            const int n0 = p0 / (p.W * p.H);
+#pragma unroll
+            for (int a = 0; a < 4; ++a) tma_load_2d_pair(sa + a * 4096, &mapA, lbar, m_tile * 128 + a * 32, p0);
+#pragma unroll
+            for (int j = 0; j < kHalfAtoms; ++j)
+              tma_load_4d_pair(sb + j * 4096, &mapB, lbar, n_tile * NT + (crank * kHalfAtoms + j) * 32, w0 + sx - 1,
+                               h0 + r - 1, n0);
+          }
+          continue;
+        }
+        mbar_arrive_expect_tx(&full_bar[s], S::kStageBytes);
         if (MODE == kFprop) {
           const int tap = kk / cpt, cc = kk - tap * cpt;
           const int r = tap / 3, sx = tap - 3 * r;
@@ -194,7 +250,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    constexpr uint32_t idesc = umma_idesc_tf32(NT, A_MN, B_MN);
+    constexpr uint32_t idesc = umma_idesc_tf32(NT, A_MN, B_MN, G == 2 ? 256 : 128);
     // K-major (SWIZZLE_128B): 8-row groups 1024 B apart (SBO), LBO unused.
     // MN-major (SWIZZLE_128B_BASE32B): smem is [K rows][128 B of MN]; 4-row K groups 512 B apart (SBO), 32-element MN
     // atoms one 32-row block (4096 B) apart (LBO).
@@ -202,10 +258,15 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     constexpr uint32_t b_lbo = B_MN ? 4096 : 16, b_sbo = B_MN ? 512 : 1024, b_lt = B_MN ? 1 : 2;
     constexpr uint32_t a_kstep = A_MN ? 1024 : 32;  // bytes per UMMA k-step (8 tf32)
     constexpr uint32_t b_kstep = B_MN ? 1024 : 32;
-    for (int i = 0; i < k_count; ++i) {
+    // bring-up aid: with a debug buffer, CTA (gridDim.x/2, 0, 0) reports where its issuer thread spends its cycles
+    const bool timing = p.debug_dump != nullptr && blockIdx.x == gridDim.x / 2 && blockIdx.y == 0 && blockIdx.z == 0;
+    long long t_wait = 0, t_begin = timing ? clock64() : 0;
+    for (int i = 0; i < (leader ? k_count : 0); ++i) {  // pair: only the leader CTA issues
       const int s = i % STAGES;
       const uint32_t ph = (i / STAGES) & 1;
+      const long long tw0 = timing ? clock64() : 0;
       mbar_wait(&full_bar[s], ph, 200 + s);
+      if (timing) t_wait += clock64() - tw0;
       tc_fence_after();
       if (p.debug_dump != nullptr && i == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
         const float* src = reinterpret_cast<const float*>(stage_base);  // bring-up aid: raw stage 0 (A then B)
@@ -219,18 +280,30 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         for (int ks = 0; ks < 4; ++ks) {
           const uint64_t ad = umma_smem_desc(sa + ks * a_kstep, a_lbo, a_sbo, a_lt);
           const uint64_t bd = umma_smem_desc(sb + ks * b_kstep, b_lbo, b_sbo, b_lt);
-          umma_tf32(tmem_acc, ad, bd, idesc, (i > 0 || ks > 0) ? 1u : 0u);
+          if (G == 2) umma_tf32_pair(tmem_acc, ad, bd, idesc, (i > 0 || ks > 0) ? 1u : 0u);
+          else umma_tf32(tmem_acc, ad, bd, idesc, (i > 0 || ks > 0) ? 1u : 0u);
         }
         // frees the smem slot when these MMAs retire (in every CTA of the cluster: peers write our B slice too)
-        if (CL == 1) umma_commit(&empty_bar[s]);
+        if (G == 2) umma_commit_pair_mc(&empty_bar[s], 3);
+        else if (CL == 1) umma_commit(&empty_bar[s]);
         else umma_commit_mc(&empty_bar[s], kClusterMask);
-        if (i == k_count - 1) umma_commit(acc_bar);  // accumulator complete
+        if (i == k_count - 1) {  // accumulator complete (in both CTAs of a pair)
+          if (G == 2) umma_commit_pair_mc(acc_bar, 3);
+          else umma_commit(acc_bar);
+        }
       }
       __syncwarp();
+    }
+    if (timing && lane == 0) {  // [12288..): cycles waiting for operands, cycles in the main loop, k iterations
+      p.debug_dump[12288] = (float)t_wait;
+      p.debug_dump[12289] = (float)(clock64() - t_begin);
+      p.debug_dump[12290] = (float)k_count;
+      p.debug_dump[12293] = (float)(t_begin - c_entry);  // prologue: barriers, TMEM allocation, first block barrier
     }
   } else {
     // ------------------------------------------------------------------ epilogue warps (2..5)
     pdl_wait();  // outputs / workspace may still be in use by the previous kernel
+    const long long e_begin = clock64();
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     float* tile = staging + q * (32 * 33);
     const int row_base = m_tile * 128 + q * 32;
@@ -242,6 +315,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
       mbar_wait(acc_bar, 0, 300);
       tc_fence_after();
     }
+    const long long e_acc = clock64();
     float csum = 0.f, csq = 0.f;
 #pragma unroll 1
     for (int c0 = 0; c0 < NT; c0 += 32) {
@@ -303,16 +377,31 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
       }
     }
     // split-K: the partial tile is in the workspace; splitk_reduce_kernel (next launch) finishes the job
+    if (p.debug_dump != nullptr && blockIdx.x == gridDim.x / 2 && blockIdx.y == 0 && blockIdx.z == 0 &&
+        threadIdx.x == 64) {  // bring-up aid: cycles until the accumulator was ready, cycles of the epilogue
+      p.debug_dump[12291] = (float)(e_acc - e_begin);
+      p.debug_dump[12292] = (float)(clock64() - e_acc);
+    }
   }
 
   __syncwarp();  // re-converge the single-lane producer / issuer warps before the aligned barrier
   tc_fence_before();
   // a CTA must not retire while a peer's commit can still arrive on its barriers
-  if (CL > 1) cluster_sync_all();
+  if (CL > 1 || G == 2) cluster_sync_all();
   else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<NT>(tmem_acc);
+    if (G == 2) tmem_dealloc_pair<NT>(tmem_acc);
+    else tmem_dealloc<NT>(tmem_acc);
+  }
+  if (trace_cta) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    reinterpret_cast<unsigned*>(p.debug_dump)[12800 + 3 * cta_linear + 1] = (unsigned)t;
+    if (blockIdx.x == gridDim.x / 2 && blockIdx.y == 0 && blockIdx.z == 0) {
+      p.debug_dump[12294] = (float)(clock64() - c_entry);  // SM cycles entry -> exit of the timed CTA
+      p.debug_dump[12295] = (float)(unsigned)(t - (unsigned long long)reinterpret_cast<unsigned*>(p.debug_dump)[12800 + 3 * cta_linear]);
+    }
   }
 }
 

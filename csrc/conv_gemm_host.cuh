@@ -114,9 +114,46 @@ int launch_conv_gemm_cl(const CUtensorMap& mA, const CUtensorMap& mB, const Conv
   return 0;
 }
 
+// CTA-pair variant (cta_group::2): cluster (2,1,1), each CTA stages half of B.  cl == kPairMode selects it.
+constexpr int kPairMode = -2;
+template <int MODE, int NT>
+int launch_conv_gemm_pair(const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
+                          cudaStream_t stream) {
+  constexpr int STAGES = (NT == 256) ? 3 : 4;  // per-CTA stage: 16 KB A + NT/2 x 128 B of B -> ~96 KB, two CTAs per SM
+  using S = ConvGemmSmem<NT, STAGES, 2>;
+  auto kern = conv_gemm_kernel<MODE, NT, STAGES, 1, 2>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DPB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(192);
+  cfg.dynamicSmemBytes = S::kTotal;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  DPB_CUDA(cudaLaunchKernelEx(&cfg, kern, mA, mB, p));
+  g_conv_last_launches = p.splits > 1 ? 2 : 1;
+  if (p.splits > 1) {
+    const int m_tiles = grid.x, n_tiles = grid.y;
+    const int tiles = m_tiles * n_tiles * (MODE == kWgrad ? 9 : 1);
+    const int pieces = splitk_pieces(tiles, m_tiles, NT);
+    DPB_CUDA(launch_k(splitk_reduce_kernel<MODE>, dim3(tiles, pieces), dim3(256), 0, stream, p, NT, m_tiles, n_tiles, pieces));
+  }
+  return 0;
+}
+
 template <int MODE, int NT>
 int launch_conv_gemm_nt(int cl, const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
                         cudaStream_t stream) {
+  if (cl == kPairMode) return launch_conv_gemm_pair<MODE, NT>(mA, mB, p, grid, stream);
   if (cl == 2) return launch_conv_gemm_cl<MODE, NT, 2>(mA, mB, p, grid, stream);
   if constexpr (NT >= 128) {
     if (cl == 4) return launch_conv_gemm_cl<MODE, NT, 4>(mA, mB, p, grid, stream);
@@ -136,8 +173,11 @@ int launch_conv_gemm_mode(int nt, int cl, const CUtensorMap& mA, const CUtensorM
 }
 
 // Cluster size along M for B-tile multicast: the largest of {tuned value, 2, 1} that divides the M tiles and the B atoms.
+// g_tune_pair: use CTA pairs (cta_group::2) whenever the M tiles come in twos; returns kPairMode then.
 inline int g_tune_cluster = 1;
+inline int g_tune_pair = 0;
 inline int pick_cluster(int m_tiles, int nt) {
+  if (g_tune_pair && m_tiles % 2 == 0 && (nt / 32) % 2 == 0) return kPairMode;
   int cl = g_tune_cluster;
   while (cl > 1 && (m_tiles % cl != 0 || (nt / 32) % cl != 0)) cl >>= 1;
   return cl < 1 ? 1 : cl;
@@ -213,7 +253,8 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
     if (mode == kFprop) {
       cuuint64_t dims[2] = {(cuuint64_t)9 * g.cin, (cuuint64_t)g.cout};
       cuuint64_t str[1] = {(cuuint64_t)9 * g.cin * 4};
-      cuuint32_t box[2] = {32, (cuuint32_t)(nt / cl)};  // each CTA of a cluster fetches (and multicasts) nt/cl rows
+      // each CTA of a multicast cluster fetches nt/cl rows; each CTA of a pair stages nt/2 rows
+      cuuint32_t box[2] = {32, (cuuint32_t)(cl == kPairMode ? nt / 2 : nt / cl)};
       if ((rc = make_map_f32(&mB, w, 2, dims, str, box))) return rc;
     } else {
       cuuint64_t dims[2] = {(cuuint64_t)9 * g.cin, (cuuint64_t)g.cout};

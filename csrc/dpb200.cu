@@ -55,6 +55,7 @@ int dpb_set_tuning(int key, int value) {
   if (key == 3 && value >= 1) { g_tune_min_k_iters = value; return 0; }
   if (key == 4) { g_tune_use_pdl = value ? 1 : 0; return 0; }
   if (key == 5 && (value == 1 || value == 2 || value == 4)) { g_tune_cluster = value; return 0; }
+  if (key == 6) { g_tune_pair = value ? 1 : 0; return 0; }
   return set_error(-30, "dpb_set_tuning: bad key/value %d/%d", key, value);
 }
 
@@ -505,6 +506,14 @@ int dpb_reducer_mark_ready(dpb_reducer* r, int param, dpb_stream_t main_stream) 
                          /*algo=*/0, /*blocks=*/0, r->side);
   if (rc) return rc;
   r->launched++;
+  return 0;
+}
+
+int dpb_reducer_wait_stream(dpb_reducer* r, dpb_stream_t producer) {
+  // gradients of the next buckets may come from a second compute stream (weight gradients overlapped with the
+  // data-gradient chain): every reduction launched from now on also waits for what that stream holds at this point
+  DPB_CUDA(cudaEventRecord(r->ev_ready, S(producer)));
+  DPB_CUDA(cudaStreamWaitEvent(r->side, r->ev_ready, 0));
   return 0;
 }
 

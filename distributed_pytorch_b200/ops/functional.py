@@ -102,7 +102,17 @@ class _ConvBnReluPool(torch.autograd.Function):
         if ctx.first:
             K.first_conv_wgrad(xin, dy, d_conv_w)
         else:
-            K.conv3x3_gemm(2, n, h, w, cin, cout, dy, xin, wk, d_conv_w)
+            # the weight gradient feeds nothing further down the chain: run it next to the data gradient (and the
+            # previous block's BatchNorm backward) on the device's second stream.  Only when autograd will adopt the
+            # result without launching an accumulation kernel on this stream (param.grad is None).
+            if K.wgrad_overlap() and conv_w.grad is None and ctx.needs_input_grad[0]:
+                lane = K.wgrad_lane(y.device)
+                lane.fork()
+                with torch.cuda.stream(lane.stream):
+                    K.conv3x3_gemm(2, n, h, w, cin, cout, dy, xin, wk, d_conv_w, side=True)
+                lane.hold(dy, xin)  # not d_conv_w: AccumulateGrad only adopts a gradient nobody else references
+            else:
+                K.conv3x3_gemm(2, n, h, w, cin, cout, dy, xin, wk, d_conv_w)
             if ctx.needs_input_grad[0]:
                 dx = K.nhwc_empty(n, cin, h, w, y.device)
                 K.conv3x3_gemm(1, n, h, w, cin, cout, dy, None, wk, dx)

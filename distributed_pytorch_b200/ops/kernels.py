@@ -7,6 +7,7 @@ enqueues on ``torch.cuda.current_stream()`` and returns immediately.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional
 
 import torch
@@ -41,6 +42,10 @@ class Scratch:
         self.device = device
         self.conv_ws = torch.empty(lib.dpb_conv_workspace_bytes() // 4, device=device, dtype=torch.float32)
         self.conv_counters = torch.zeros(lib.dpb_conv_counter_bytes() // 4, device=device, dtype=torch.int32)
+        # second split-K workspace: weight-gradient GEMMs running on the side stream (WgradLane) must not share partial
+        # tiles with the data-gradient GEMM that runs next to them
+        self.conv_ws_side = None
+        self.conv_counters_side = None
         self.bn_blocks = lib.dpb_bn_bwd_blocks()
         self.bn_part = torch.empty(2 * self.bn_blocks * 1024, device=device, dtype=torch.float32)
         self.bn_coef = torch.empty(3 * 1024, device=device, dtype=torch.float32)
@@ -59,13 +64,95 @@ def scratch(device: torch.device) -> Scratch:
     return s
 
 
+class WgradLane:
+    """Second compute stream of a device for weight-gradient kernels.
+
+    In backward, a layer's weight gradient depends only on that layer's ``dY`` and saved input, while the chain that
+    continues backward is data-gradient GEMM -> previous layer's BatchNorm/ReLU/pool backward (memory-bound) -> ...
+    Running the weight-gradient GEMM (+ its split-K reduce) on its own stream lets it fill the SMs the chain leaves idle:
+    wave tails, epilogues, the elementwise kernels.  The reference's backward (cuDNN through autograd) is single-stream.
+
+    ``fork()`` orders the lane after the current stream, ``hold()`` keeps the kernels' inputs alive (they were allocated
+    on the main stream, so the caching allocator must not hand them out again before the lane is done), ``join()`` makes
+    the current stream wait for the lane and drops the references.  ``join`` is queued as an autograd end-of-backward
+    callback by the first fork of a backward pass, so ``.grad`` is safe to read on the main stream after ``backward()``;
+    consumers that run earlier (the DDP reducer) call ``pending`` / ``stream`` themselves.
+    """
+
+    def __init__(self, device: torch.device):
+        self.device = device
+        self.stream = torch.cuda.Stream(device=device)
+        self._fork_ev = torch.cuda.Event()
+        self._join_ev = torch.cuda.Event()
+        self._held: list = []
+        self.pending = False
+        self._callback_queued = False
+        sc = scratch(device)
+        if sc.conv_ws_side is None:
+            sc.conv_ws_side = torch.empty_like(sc.conv_ws)
+            sc.conv_counters_side = torch.zeros_like(sc.conv_counters)
+
+    def fork(self) -> None:
+        self._fork_ev.record(torch.cuda.current_stream(self.device))
+        self.stream.wait_event(self._fork_ev)
+        self.pending = True
+        if not self._callback_queued:
+            torch.autograd.Variable._execution_engine.queue_callback(self.join)
+            self._callback_queued = True
+
+    def hold(self, *tensors) -> None:
+        self._held.extend(tensors)
+
+    def join(self) -> None:
+        self._callback_queued = False
+        if self.pending:
+            self._join_ev.record(self.stream)
+            torch.cuda.current_stream(self.device).wait_event(self._join_ev)
+            self.pending = False
+        self._held.clear()
+
+
+_lanes: dict[int, WgradLane] = {}
+_wgrad_overlap = os.environ.get("DPB_WGRAD_OVERLAP", "0") == "1"
+
+
+def set_wgrad_overlap(enabled: bool) -> None:
+    """Weight-gradient kernels on a second stream (``DPB_WGRAD_OVERLAP=1``).  Off by default: measured on B200 it is
+    neutral at batch 256 (1.0741 vs 1.0736 ms/step) and +1.3 % at batch 32 -- both conv CTA slots of every SM are
+    already taken by the data-gradient GEMM, so the second stream only fills wave tails."""
+    global _wgrad_overlap
+    _wgrad_overlap = bool(enabled)
+
+
+def wgrad_overlap() -> bool:
+    return _wgrad_overlap
+
+
+def wgrad_lane(device: torch.device) -> WgradLane:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    lane = _lanes.get(idx)
+    if lane is None:
+        lane = WgradLane(torch.device("cuda", idx))
+        _lanes[idx] = lane
+    return lane
+
+
+def active_wgrad_lane(device: torch.device) -> Optional[WgradLane]:
+    """The device's lane if it holds work the current stream has not been ordered after yet."""
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    lane = _lanes.get(idx)
+    return lane if lane is not None and lane.pending else None
+
+
 def conv3x3_gemm(mode: int, n: int, h: int, w: int, cin: int, cout: int, inp: torch.Tensor,
                  inp2: Optional[torch.Tensor], weight: torch.Tensor, out: torch.Tensor,
-                 bias: Optional[torch.Tensor] = None, want_stats: bool = False, nt: int = 0, splits: int = 0):
+                 bias: Optional[torch.Tensor] = None, want_stats: bool = False, nt: int = 0, splits: int = 0,
+                 side: bool = False):
     """tcgen05 implicit-GEMM conv. mode 0 fprop / 1 dgrad / 2 wgrad. Returns (stat_sum, stat_sq, m_tiles) for fprop
-    with ``want_stats`` else None."""
+    with ``want_stats`` else None.  ``side`` selects the second split-K workspace (see :class:`WgradLane`)."""
     lib = N.require()
     sc = scratch(out.device)
+    conv_ws, conv_counters = (sc.conv_ws_side, sc.conv_counters_side) if side else (sc.conv_ws, sc.conv_counters)
     stat_sum = stat_sq = None
     m_tiles = ctypes.c_int(0)
     if want_stats:
@@ -74,8 +161,8 @@ def conv3x3_gemm(mode: int, n: int, h: int, w: int, cin: int, cout: int, inp: to
         stat_sum = torch.empty((tiles, cout), device=out.device, dtype=torch.float32)
         stat_sq = torch.empty((tiles, cout), device=out.device, dtype=torch.float32)
     N.check(lib.dpb_conv3x3_gemm(mode, n, h, w, cin, cout, N.ptr(inp), N.ptr(inp2), N.ptr(weight), N.ptr(out),
-                                 N.ptr(bias), N.ptr(stat_sum), N.ptr(stat_sq), N.ptr(sc.conv_ws),
-                                 N.ptr(sc.conv_counters), nt, splits, ctypes.byref(m_tiles), N.stream()),
+                                 N.ptr(bias), N.ptr(stat_sum), N.ptr(stat_sq), N.ptr(conv_ws),
+                                 N.ptr(conv_counters), nt, splits, ctypes.byref(m_tiles), N.stream()),
             "dpb_conv3x3_gemm")
     N.count_launches(lib.dpb_conv_last_launches())
     if want_stats:

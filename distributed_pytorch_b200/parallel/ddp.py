@@ -27,6 +27,7 @@ import torch.distributed as dist
 import torch.nn as nn
 
 from .. import _native as N
+from ..ops import kernels as K
 from ..utils.arena import FlatArena
 from .comm import Communicator, SymmetricBuffer
 
@@ -232,6 +233,10 @@ class DistributedDataParallel(nn.Module):
                 v = self.arena.grad_view(pos)
                 v.copy_(param.grad)
                 param.grad = v
+            lane = K.active_wgrad_lane(param.device)
+            if lane is not None:  # weight gradients computed on the second compute stream: the reduction waits for it too
+                N.check(N.require().dpb_reducer_wait_stream(self._reducer, lane.stream.cuda_stream),
+                        "dpb_reducer_wait_stream")
             N.check(N.require().dpb_reducer_mark_ready(self._reducer, pos, N.stream()), "dpb_reducer_mark_ready")
             return
         b = self.bucket_of_param[i]

@@ -152,6 +152,9 @@ int dpb_reducer_prepare(dpb_reducer* r);
 /* Called from the autograd post-accumulate hook of parameter `param`; launches the bucket's all-reduce on the side
  * stream once its last gradient is ready. */
 int dpb_reducer_mark_ready(dpb_reducer* r, int param, dpb_stream_t main_stream);
+/* Bucket reductions launched after this call also wait for the work `producer` holds now (weight gradients computed on
+ * a second compute stream).  No counterpart in the reference: its backward is single-stream. */
+int dpb_reducer_wait_stream(dpb_reducer* r, dpb_stream_t producer);
 /* Makes main_stream wait for every outstanding bucket. */
 int dpb_reducer_finalize(dpb_reducer* r, dpb_stream_t main_stream);
 int dpb_reducer_launched(dpb_reducer* r); /* buckets launched since the last prepare */

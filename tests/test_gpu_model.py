@@ -88,6 +88,34 @@ def test_training_trajectory_and_graph_step():
         assert torch.allclose(p, q, rtol=1e-5, atol=1e-6), k
 
 
+def test_wgrad_second_stream_is_bit_identical():
+    """Weight gradients on the second compute stream (K.WgradLane): same kernels, so eager and captured steps must
+    reproduce the single-stream run bit for bit, and gradients must still land in the arena in place."""
+    from distributed_pytorch_b200.ops import kernels as K
+    _, base = _pair(5)
+    lane = copy.deepcopy(base)
+    arena_a, arena_b = adopt_module(base), adopt_module(lane)
+    oa = dpb.SGD(base.parameters(), lr=0.02, momentum=0.9, weight_decay=1e-4)
+    ob = dpb.SGD(lane.parameters(), lr=0.02, momentum=0.9, weight_decay=1e-4)
+    sa = dpb.TrainStep(base, oa, use_graph=True, warmup=2)
+    sb = dpb.TrainStep(lane, ob, use_graph=True, warmup=2)
+    g = torch.Generator().manual_seed(11)
+    try:
+        for _ in range(5):
+            x, y = torch.randn(32, 3, 32, 32, generator=g).pin_memory(), torch.randint(0, 10, (32,), generator=g).pin_memory()
+            K.set_wgrad_overlap(False)
+            la = sa(x, y).item()
+            K.set_wgrad_overlap(True)
+            lb = sb(x, y).item()
+            assert la == lb
+        assert sb.replays >= 2 and arena_b.grads_in_place()
+        torch.cuda.synchronize()
+        assert torch.equal(arena_a.param_buf, arena_b.param_buf)
+        assert torch.equal(arena_a.grad_buf, arena_b.grad_buf)
+    finally:
+        K.set_wgrad_overlap(False)
+
+
 def test_eval_mode_and_metrics():
     cpu, gpu = _pair(3)
     cpu.eval()
