@@ -47,12 +47,12 @@ struct ConvGemmSmem {
   static constexpr int kABytes = 128 * 128;  // 128 rows x 32 tf32
   static constexpr int kBBytes = NT * 128 / G;  // CTA pair (G = 2): each CTA holds half of the B tile
   static constexpr int kStageBytes = kABytes + kBBytes;
-  // The epilogue's per-warp 32x33 fp32 transpose tiles (4 * 32 * 33 * 4 = 16.5 KB) reuse stage 0: by the time the
-  // accumulator barrier fires every TMA load has landed and every MMA has finished reading shared memory.  Keeping the
-  // footprint at ~100 KB (NT <= 128) lets two CTAs share an SM, so one CTA's prologue / epilogue overlaps the other's
-  // main loop.
-  static constexpr int kStagingBytes = 4 * 32 * 33 * 4;
-  static_assert(kStagingBytes <= kStageBytes, "staging must fit in one pipeline stage");
+  // The epilogue stages the whole 128 x NT fp32 tile row-major (one 32 x NT slab per warp, 16-byte chunks XOR-swizzled
+  // by row so both the column-wise writes out of TMEM and the row-wise reads are bank-conflict free) and reuses the
+  // pipeline stages for it: by the time the accumulator barrier fires every TMA load has landed and every MMA has
+  // finished reading shared memory.  Keeping the footprint at ~100 KB (NT <= 128) lets two CTAs share an SM.
+  static constexpr int kStagingBytes = 128 * NT * 4;
+  static_assert(kStagingBytes <= STAGES * kStageBytes, "staging must fit in the pipeline stages");
   static constexpr int kBarBytes = 256;
   static constexpr int kTotal = 1024 /*align slack*/ + STAGES * kStageBytes + kBarBytes + 2 * NT * 4 * 4;
 };
@@ -305,7 +305,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     pdl_wait();  // outputs / workspace may still be in use by the previous kernel
     const long long e_begin = clock64();
     const int q = warp & 3;  // TMEM lane quarter this warp may read
-    float* tile = staging + q * (32 * 33);
+    float* tile = staging + q * (32 * NT);
     const int row_base = m_tile * 128 + q * 32;
     const int tile_id = ((MODE == kWgrad ? wtap : 0) * gridDim.y + n_tile) * gridDim.x + m_tile;
     float* ws = nullptr;
@@ -316,7 +316,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
       tc_fence_after();
     }
     const long long e_acc = clock64();
-    float csum = 0.f, csq = 0.f;
+    // TMEM -> registers (lane = accumulator row, 32 columns per load) -> this warp's 32 x NT slab, row-major with the
+    // 16-byte chunk index XORed by (row & 7): a quarter warp's STS.128 (8 rows, same logical chunk) hits 8 distinct
+    // bank groups, and so does a row-wise LDS.128 below.
+    constexpr int kChunks = NT / 4;  // 16-byte chunks per tile row
 #pragma unroll 1
     for (int c0 = 0; c0 < NT; c0 += 32) {
       float v[32];
@@ -327,36 +330,70 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         for (int j = 0; j < 32; ++j) v[j] = 0.f;
       }
 #pragma unroll
-      for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = v[j];
-      __syncwarp();
-      const int col = n_tile * NT + c0 + lane;
-      if (p.splits > 1) {
-#pragma unroll 4
-        for (int i = 0; i < 32; ++i) ws[(size_t)(q * 32 + i) * NT + c0 + lane] = tile[i * 33 + lane];
-      } else {
-        float b = 0.f;
-        if (MODE == kFprop && p.bias != nullptr) b = p.bias[col];
-        float* orow;
-        if (MODE == kWgrad)
-          orow = p.out + (size_t)row_base * p.out_ld + (size_t)wtap * p.CinW + col;
-        else
-          orow = p.out + (size_t)row_base * p.out_ld + col;
-        csum = 0.f; csq = 0.f;
-#pragma unroll 4
-        for (int i = 0; i < 32; ++i) {
-          if (row_base + i < p.M_total) {
-            const float y = tile[i * 33 + lane] + b;
-            orow[(size_t)i * p.out_ld] = y;
-            csum += y;
-            csq += y * y;
+      for (int j = 0; j < 8; ++j) {
+        const int chunk = (c0 >> 2) + j;
+        *reinterpret_cast<float4*>(tile + lane * NT + ((chunk ^ (lane & 7)) << 2)) =
+            make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      }
+    }
+    __syncwarp();
+    // slab -> global: every store instruction writes whole rows (512 B of one row at NT = 128, two rows at NT = 64)
+    constexpr int kIters = 32 * kChunks / 32;                // float4 per lane
+    constexpr int kSets = kChunks > 32 ? kChunks / 32 : 1;   // distinct column groups a lane meets (NT = 256: two)
+    float4 csum[kSets], csq[kSets];
+#pragma unroll
+    for (int s = 0; s < kSets; ++s) csum[s] = csq[s] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.splits > 1) {
+      float4* dst = reinterpret_cast<float4*>(ws + (size_t)(q * 32) * NT);
+#pragma unroll 8
+      for (int it = 0; it < kIters; ++it) {
+        const int idx = it * 32 + lane, row = idx / kChunks, chunk = idx % kChunks;
+        dst[idx] = *reinterpret_cast<const float4*>(tile + row * NT + ((chunk ^ (row & 7)) << 2));
+      }
+    } else {
+      const bool stats = MODE == kFprop && p.stat_sum != nullptr;
+      float* obase = p.out + (size_t)row_base * p.out_ld + (size_t)(MODE == kWgrad ? wtap * p.CinW : 0) + n_tile * NT;
+#pragma unroll 8
+      for (int it = 0; it < kIters; ++it) {
+        const int idx = it * 32 + lane, row = idx / kChunks, chunk = idx % kChunks;
+        float4 y = *reinterpret_cast<const float4*>(tile + row * NT + ((chunk ^ (row & 7)) << 2));
+        if (MODE == kFprop && p.bias != nullptr) {
+          const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n_tile * NT) + chunk);
+          y.x += b.x; y.y += b.y; y.z += b.z; y.w += b.w;
+        }
+        if (row_base + row < p.M_total) {
+          *reinterpret_cast<float4*>(obase + (size_t)row * p.out_ld + (chunk << 2)) = y;
+          if (stats) {
+            float4& s = csum[it % kSets];
+            float4& t = csq[it % kSets];
+            s.x += y.x; s.y += y.y; s.z += y.z; s.w += y.w;
+            t.x += y.x * y.x; t.y += y.y * y.y; t.z += y.z * y.z; t.w += y.w * y.w;
           }
         }
-        if (MODE == kFprop && p.stat_sum != nullptr) {
-          colred[(q * 2 + 0) * NT + c0 + lane] = csum;
-          colred[(q * 2 + 1) * NT + c0 + lane] = csq;
+      }
+      if (stats) {
+        if (kChunks < 32) {  // NT = 64: lanes l and l + 16 hold the same columns (even / odd rows)
+#pragma unroll
+          for (int off = kChunks; off < 32; off <<= 1) {
+            csum[0].x += __shfl_xor_sync(0xffffffffu, csum[0].x, off);
+            csum[0].y += __shfl_xor_sync(0xffffffffu, csum[0].y, off);
+            csum[0].z += __shfl_xor_sync(0xffffffffu, csum[0].z, off);
+            csum[0].w += __shfl_xor_sync(0xffffffffu, csum[0].w, off);
+            csq[0].x += __shfl_xor_sync(0xffffffffu, csq[0].x, off);
+            csq[0].y += __shfl_xor_sync(0xffffffffu, csq[0].y, off);
+            csq[0].z += __shfl_xor_sync(0xffffffffu, csq[0].z, off);
+            csq[0].w += __shfl_xor_sync(0xffffffffu, csq[0].w, off);
+          }
+        }
+#pragma unroll
+        for (int s = 0; s < kSets; ++s) {
+          const int chunk = s * 32 + lane;
+          if (chunk < kChunks) {
+            *reinterpret_cast<float4*>(colred + (q * 2 + 0) * NT + (chunk << 2)) = csum[s];
+            *reinterpret_cast<float4*>(colred + (q * 2 + 1) * NT + (chunk << 2)) = csq[s];
+          }
         }
       }
-      __syncwarp();
     }
     tc_fence_before();
     // named barrier over the 128 epilogue threads

@@ -119,7 +119,7 @@ constexpr int kPairMode = -2;
 template <int MODE, int NT>
 int launch_conv_gemm_pair(const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
                           cudaStream_t stream) {
-  constexpr int STAGES = (NT == 256) ? 3 : 4;  // per-CTA stage: 16 KB A + NT/2 x 128 B of B -> ~96 KB, two CTAs per SM
+  constexpr int STAGES = 4;  // per-CTA stage: 16 KB A + NT/2 x 128 B of B (NT 128: 96 KB, NT 256: 128 KB = the staged tile)
   using S = ConvGemmSmem<NT, STAGES, 2>;
   auto kern = conv_gemm_kernel<MODE, NT, STAGES, 1, 2>;
   static bool attr_set = false;
