@@ -11,6 +11,7 @@
 #include "conv_gemm_host.cuh"
 #include "bn_relu_pool.cuh"
 #include "first_conv.cuh"
+#include "first_conv_tc.cuh"
 #include "head_sgd.cuh"
 #include "comm.cuh"
 
@@ -21,6 +22,7 @@ int g_tune_comm_blocks = 64;  // default grid cap of the collective kernels (dpb
 inline cudaStream_t S(dpb_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 constexpr int kBnBwdBlocks = 296;
 constexpr int kFirstWgradBlocks = 296;
+int g_tune_first_tc = 1;  // first layer on the tensor cores when the image shape allows (dpb_set_tuning key 7)
 inline int grid_for(long long units, int threads, int cap) {
   long long b = (units + threads - 1) / threads;
   if (b > cap) b = cap;
@@ -56,6 +58,7 @@ int dpb_set_tuning(int key, int value) {
   if (key == 4) { g_tune_use_pdl = value ? 1 : 0; return 0; }
   if (key == 5 && (value == 1 || value == 2 || value == 4)) { g_tune_cluster = value; return 0; }
   if (key == 6) { g_tune_pair = value ? 1 : 0; return 0; }
+  if (key == 7) { g_tune_first_tc = value ? 1 : 0; return 0; }
   return set_error(-30, "dpb_set_tuning: bad key/value %d/%d", key, value);
 }
 
@@ -75,7 +78,10 @@ int dpb_conv3x3_gemm(int mode, int n, int h, int w, int cin, int cout, const flo
 }
 
 int dpb_first_conv_blocks(int n, int h, int w) {
-  (void)w;
+  if (g_tune_first_tc && first_conv_tc_supported(h, w)) {
+    const long long tiles = (long long)n * h * w / 128;
+    return (int)(tiles < kFcTcMaxBlocks ? tiles : kFcTcMaxBlocks);
+  }
   const long long b = (long long)n * ((h + kFcRows - 1) / kFcRows);  // tiles of kFcRows image rows
   return (int)(b < kFirstConvMaxBlocks ? b : kFirstConvMaxBlocks);
 }
@@ -87,8 +93,17 @@ static int first_conv_check(int w) {
 
 int dpb_first_conv_fprop(const float* x, const float* weight, const float* bias, float* y, float* part_sum,
                          float* part_sq, int n, int h, int w, dpb_stream_t stream) {
-  if (int rc = first_conv_check(w)) return rc;
   const int blocks = dpb_first_conv_blocks(n, h, w);
+  if (g_tune_first_tc && first_conv_tc_supported(h, w)) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      DPB_CUDA(cudaFuncSetAttribute(first_conv_fprop_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FcTcSmem::kTotal));
+      attr_set = true;
+    }
+    DPB_CUDA(launch_k(first_conv_fprop_tc_kernel, dim3(blocks), dim3(kFcTcThreads), FcTcSmem::kTotal, S(stream), x, weight, bias, y, part_sum, part_sq, n, h, w));
+    return 0;
+  }
+  if (int rc = first_conv_check(w)) return rc;
   DPB_CUDA(launch_k(first_conv_fprop_kernel, dim3(blocks), dim3(256), 0, S(stream), x, weight, bias, y, part_sum, part_sq, n, h, w));
   return 0;
 }

@@ -111,21 +111,35 @@ def test_bn_eval_mode(K):
     assert torch.allclose(out.cpu(), ref, rtol=1e-4, atol=1e-5)
 
 
-@pytest.mark.parametrize("N", [1, 8, 33])
-def test_first_conv_fprop_and_wgrad(K, N):
+@pytest.mark.parametrize("tensor_cores", [0, 1])
+@pytest.mark.parametrize("N,HW", [(1, 32), (8, 32), (33, 32), (5, 16), (3, 64), (4, 30)])
+def test_first_conv_fprop_and_wgrad(K, N, HW, tensor_cores):
+    """Cin = 3 entry layer vs the fp32 oracle: the FP32-pipe kernels to fp32 accuracy, the tcgen05 kernels (TF32
+    operands, fp32 accumulate; 30 x 30 images do not tile into 128 pixels and take the FP32-pipe path) to TF32 accuracy."""
+    from distributed_pytorch_b200 import _native
     torch.manual_seed(4)
-    x = torch.randn(N, 3, 32, 32)
+    x = torch.randn(N, 3, HW, HW)
     w = (torch.randn(64, 3, 3, 3) * 0.2).requires_grad_(True)
     b = torch.randn(64)
     ref = F.conv2d(x, w, b, padding=1)
     dy = torch.randn_like(ref)
     ref.backward(dy)
     wd = nhwc(w.detach().cuda())
-    y = torch.empty((N, 64, 32, 32), device="cuda").contiguous(memory_format=torch.channels_last)
-    ps, pq, parts = K.first_conv_fprop(x.cuda(), wd, b.cuda(), y, True)
-    assert torch.allclose(y.cpu(), ref.detach(), rtol=1e-4, atol=1e-4)
-    assert torch.allclose(ps.sum(0).cpu(), ref.detach().sum((0, 2, 3)), rtol=1e-3, atol=1e-2)
-    assert torch.allclose(pq.sum(0).cpu(), (ref.detach() ** 2).sum((0, 2, 3)), rtol=1e-3, atol=1e-2)
-    dw = torch.empty_like(wd)
-    K.first_conv_wgrad(x.cuda(), nhwc(dy.cuda()), dw)
-    assert torch.allclose(dw.cpu(), w.grad, rtol=1e-3, atol=1e-3 * float(w.grad.abs().max()))
+    y = torch.empty((N, 64, HW, HW), device="cuda").contiguous(memory_format=torch.channels_last)
+    lib = _native.require()
+    lib.dpb_set_tuning(7, tensor_cores)
+    try:
+        ps, pq, parts = K.first_conv_fprop(x.cuda(), wd, b.cuda(), y, True)
+        dw = torch.empty_like(wd)
+        K.first_conv_wgrad(x.cuda(), nhwc(dy.cuda()), dw)
+        torch.cuda.synchronize()
+    finally:
+        lib.dpb_set_tuning(7, 1)
+    tf32 = tensor_cores and HW != 30
+    tol = 2e-3 if tf32 else 1e-4
+    refd = ref.detach()
+    assert float((y.cpu() - refd).abs().max()) <= tol * max(1.0, float(refd.abs().max()))
+    cnt = N * HW * HW
+    assert torch.allclose(ps.sum(0).cpu(), refd.sum((0, 2, 3)), rtol=1e-3, atol=1e-2 + (2e-4 * cnt if tf32 else 0))
+    assert torch.allclose(pq.sum(0).cpu(), (refd ** 2).sum((0, 2, 3)), rtol=2e-3 if tf32 else 1e-3, atol=1e-2)
+    assert torch.allclose(dw.cpu(), w.grad, rtol=1e-3, atol=(3e-3 if tf32 else 1e-3) * float(w.grad.abs().max()))
