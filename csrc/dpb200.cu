@@ -21,7 +21,7 @@ namespace {
 int g_tune_comm_blocks = 64;  // default grid cap of the collective kernels (dpb_set_tuning key 2)
 inline cudaStream_t S(dpb_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 constexpr int kBnBwdBlocks = 296;
-constexpr int kFirstWgradBlocks = 296;
+constexpr int kFirstWgradBlocks = 444;  // rows of the first-layer wgrad partials buffer (= kFcTcMaxBlocks)
 int g_tune_first_tc = 1;  // first layer on the tensor cores when the image shape allows (dpb_set_tuning key 7)
 inline int grid_for(long long units, int threads, int cap) {
   long long b = (units + threads - 1) / threads;
@@ -112,11 +112,22 @@ int dpb_first_conv_wgrad_blocks(void) { return kFirstWgradBlocks; }
 
 int dpb_first_conv_wgrad(const float* x, const float* dy, float* partials, float* dw, int n, int h, int w,
                          dpb_stream_t stream) {
+  const int nout = 64 * 27;
+  if (g_tune_first_tc && first_conv_tc_supported(h, w)) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      DPB_CUDA(cudaFuncSetAttribute(first_conv_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FcTcWgradSmem::kTotal));
+      attr_set = true;
+    }
+    const int blocks = dpb_first_conv_blocks(n, h, w);  // <= kFcTcMaxBlocks == kFirstWgradBlocks
+    DPB_CUDA(launch_k(first_conv_wgrad_tc_kernel, dim3(blocks), dim3(kFcTcThreads), FcTcWgradSmem::kTotal, S(stream), x, dy, partials, n, h, w));
+    DPB_CUDA(launch_k(column_reduce_kernel, dim3((nout + 31) / 32), dim3(32, 8), 0, S(stream), partials, blocks, nout, dw));
+    return 0;
+  }
   if (int rc = first_conv_check(w)) return rc;
   int blocks = dpb_first_conv_blocks(n, h, w);
-  if (blocks > kFirstWgradBlocks) blocks = kFirstWgradBlocks;
+  if (blocks > kFirstConvMaxBlocks) blocks = kFirstConvMaxBlocks;
   DPB_CUDA(launch_k(first_conv_wgrad_kernel, dim3(blocks), dim3(256), 0, S(stream), x, dy, partials, n, h, w));
-  const int nout = 64 * 27;
   DPB_CUDA(launch_k(column_reduce_kernel, dim3((nout + 31) / 32), dim3(32, 8), 0, S(stream), partials, blocks, nout, dw));
   return 0;
 }
