@@ -95,7 +95,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     reinterpret_cast<unsigned*>(p.debug_dump)[12800 + 3 * cta_linear + 2] = sm;
   }
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_align_1024(smem_raw);
   uint8_t* stage_base = smem;
   float* staging = reinterpret_cast<float*>(smem);  // aliases stage 0, used only after the main loop has drained
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * S::kStageBytes);

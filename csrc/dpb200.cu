@@ -12,6 +12,7 @@
 #include "bn_relu_pool.cuh"
 #include "first_conv.cuh"
 #include "first_conv_tc.cuh"
+#include "first_conv_tc_wgrad.cuh"
 #include "head_sgd.cuh"
 #include "comm.cuh"
 
@@ -119,8 +120,14 @@ int dpb_first_conv_wgrad(const float* x, const float* dy, float* partials, float
       DPB_CUDA(cudaFuncSetAttribute(first_conv_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FcTcWgradSmem::kTotal));
       attr_set = true;
     }
-    const int blocks = dpb_first_conv_blocks(n, h, w);  // <= kFcTcMaxBlocks == kFirstWgradBlocks
-    DPB_CUDA(launch_k(first_conv_wgrad_tc_kernel, dim3(blocks), dim3(kFcTcThreads), FcTcWgradSmem::kTotal, S(stream), x, dy, partials, n, h, w));
+    const long long tiles = (long long)n * h * w / 128;
+    const int blocks = (int)(tiles < kFcTcWgradMaxBlocks ? tiles : kFcTcWgradMaxBlocks);
+    CUtensorMap map_dy;
+    cuuint64_t dims[2] = {64, (cuuint64_t)tiles * 128};
+    cuuint64_t str[1] = {64 * 4};
+    cuuint32_t box[2] = {32, 128};
+    if (int rc = make_map_f32(&map_dy, dy, 2, dims, str, box, /*mn_major=*/true)) return rc;
+    DPB_CUDA(launch_k(first_conv_wgrad_tc_kernel, dim3(blocks), dim3(kFcTcThreads), FcTcWgradSmem::kTotal, S(stream), map_dy, x, partials, n, h, w));
     DPB_CUDA(launch_k(column_reduce_kernel, dim3((nout + 31) / 32), dim3(32, 8), 0, S(stream), partials, blocks, nout, dw));
     return 0;
   }

@@ -36,6 +36,41 @@ __host__ __device__ inline bool first_conv_tc_supported(int h, int w) {
   return (w == 8 || w == 16 || w == 32 || w == 64) && ((h * w) % 128 == 0);
 }
 
+constexpr int kFcTcPrefetch = (kFcTcPatchFloats + kFcTcThreads - 1) / kFcTcThreads;
+
+// Thread `tid`'s share of the haloed patch [3][R + 2][W + 2] of a tile.  The element -> (channel, row, column) split
+// does not depend on the tile, so it is done once: `off` is the element's offset from the tile's first pixel in channel
+// 0, `dh` its image row relative to the tile's first row (a huge negative number marks "always zero": halo column or no
+// element).  Per tile that leaves one add, two compares and one load per element.
+struct FcTcPatchPlan {
+  int off[kFcTcPrefetch];
+  int dh[kFcTcPrefetch];
+};
+__device__ __forceinline__ void fc_tc_plan_patch(int R, int H, int W, int tid, FcTcPatchPlan& plan) {
+  const int WP = W + 2, RP = R + 2, elems = 3 * RP * WP;
+#pragma unroll
+  for (int i = 0; i < kFcTcPrefetch; ++i) {
+    const int e = tid + i * kFcTcThreads;
+    const int ci = e / (RP * WP);
+    const int rem = e - ci * (RP * WP);
+    const int r = rem / WP, c = rem - r * WP;
+    const bool ok = e < elems && c >= 1 && c <= W;
+    plan.off[i] = ci * H * W + (r - 1) * W + (c - 1);
+    plan.dh[i] = ok ? r - 1 : -(1 << 28);
+  }
+}
+// The patch of `tile` (zero outside the image) into registers.
+__device__ __forceinline__ void fc_tc_fetch_patch(const float* __restrict__ x, int tile, int tiles_per_img, int R, int H,
+                                                  int W, const FcTcPatchPlan& plan, float (&pre)[kFcTcPrefetch]) {
+  const int n = tile / tiles_per_img, h0 = (tile - n * tiles_per_img) * R;
+  const float* base = x + (long long)n * 3 * H * W + h0 * W;
+#pragma unroll
+  for (int i = 0; i < kFcTcPrefetch; ++i) {
+    const int hh = h0 + plan.dh[i];
+    pre[i] = (hh >= 0 && hh < H) ? __ldg(base + plan.off[i]) : 0.f;
+  }
+}
+
 // x: [N][3][H][W] fp32 (NCHW).  w: [64][3][3][3] (KRSC).  y: [N*H*W][64].  part_sum / part_sq: [gridDim.x][64] or null.
 __global__ void __launch_bounds__(kFcTcThreads)
 first_conv_fprop_tc_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
@@ -43,7 +78,7 @@ first_conv_fprop_tc_kernel(const float* __restrict__ x, const float* __restrict_
                            int W) {
   pdl_prologue();
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_align_1024(smem_raw);
   float* sA = reinterpret_cast<float*>(smem + FcTcSmem::kA);
   float* sB = reinterpret_cast<float*>(smem + FcTcSmem::kB);
   float* stg = reinterpret_cast<float*>(smem + FcTcSmem::kStage);
@@ -85,19 +120,19 @@ first_conv_fprop_tc_kernel(const float* __restrict__ x, const float* __restrict_
   uint32_t phase = 0;
   float acc_stat = 0.f;  // thread t: channel t & 63 of (t < 64 ? sum : sum of squares)
 
+  float pre[kFcTcPrefetch];  // the next tile's patch, in flight during this tile's MMA and epilogue
+  FcTcPatchPlan plan;
+  fc_tc_plan_patch(R, H, W, tid, plan);
+  if ((int)blockIdx.x < tiles) fc_tc_fetch_patch(x, blockIdx.x, tiles_per_img, R, H, W, plan, pre);
   for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-    const int n = tile / tiles_per_img, h0 = (tile - n * tiles_per_img) * R;
     // 1. haloed patch [3][RP][WP], zero outside the image
-    for (int e = tid; e < elems; e += kFcTcThreads) {
-      const int ci = e / (RP * WP);
-      const int rem = e - ci * (RP * WP);
-      const int r = rem / WP, c = rem - r * WP;
-      const int hh = h0 - 1 + r, ww = c - 1;
-      float v = 0.f;
-      if (hh >= 0 && hh < H && ww >= 0 && ww < W) v = __ldg(x + ((long long)(n * 3 + ci) * H + hh) * W + ww);
-      patch[e] = v;
+#pragma unroll
+    for (int i = 0; i < kFcTcPrefetch; ++i) {
+      const int e = tid + i * kFcTcThreads;
+      if (e < elems) patch[e] = pre[i];
     }
     __syncthreads();
+    if (tile + (int)gridDim.x < tiles) fc_tc_fetch_patch(x, tile + gridDim.x, tiles_per_img, R, H, W, plan, pre);
     // 2. im2col row of my pixel, written in the MMA's swizzled K-major layout
     {
       float v[32];
@@ -180,134 +215,6 @@ first_conv_fprop_tc_kernel(const float* __restrict__ x, const float* __restrict_
   if (part_sum != nullptr) (tid < 64 ? part_sum : part_sq)[(size_t)blockIdx.x * 64 + (tid & 63)] = acc_stat;
   __syncthreads();
   if (warp == 0) tmem_dealloc<64>(tmem);
-}
-
-// ---------------------------------------------------------------------------------------------------------------- wgrad
-// dW[co][k] = sum over pixels of dY[pix][co] * patch[pix][k], as the GEMM  D[k][co] = P^T[k][pix] * dY[pix][co]:
-// M = k (27 of 32 used), N = 64 channels, GEMM-K = pixels.  Both operands have the GEMM-K index (the pixel) as their
-// slow memory axis, i.e. they are MN-major, which for tf32 means the SWIZZLE_128B_BASE32B layout: a 32-pixel K block
-// of an operand atom is [32 rows][128 B], 32-byte unit u of row r stored at unit u ^ (r & 3).  The im2col rows the
-// threads write for fprop are exactly the A atom; dY rows (64 channels = 256 B) are two B atoms.  tcgen05.mma has no
-// M = 32, so the instruction runs at M = 128 with the three upper A atoms pointing at whatever follows in shared
-// memory (finite numbers: later pixels, then dY) -- accumulator rows 32..127 are never read.  One TMEM accumulator
-// lives across all tiles of the CTA (the tensor core does the reduction over pixels); every CTA writes one
-// [64 x 27] partial, summed in a fixed order by column_reduce_kernel.
-struct FcTcWgradSmem {
-  static constexpr int kA = 0;                   // 4 K blocks x [32 pixels][32 k]
-  static constexpr int kB = 16384;               // 4 K blocks x 2 atoms x [32 pixels][32 co]
-  static constexpr int kPatch = kB + 32768;
-  static constexpr int kBar = kPatch + kFcTcPatchFloats * 4;
-  static constexpr int kTotal = 1024 + kBar + 64;
-};
-
-// x: [N][3][H][W] (NCHW), dy: [N*H*W][64], partials: [gridDim.x][64*27]
-__global__ void __launch_bounds__(kFcTcThreads)
-first_conv_wgrad_tc_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ partials, int N,
-                           int H, int W) {
-  pdl_prologue();
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sA = smem + FcTcWgradSmem::kA;
-  uint8_t* sB = smem + FcTcWgradSmem::kB;
-  float* patch = reinterpret_cast<float*>(smem + FcTcWgradSmem::kPatch);
-  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + FcTcWgradSmem::kBar);
-  uint32_t* slot = reinterpret_cast<uint32_t*>(smem + FcTcWgradSmem::kBar + 8);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  if (tid == 0) {
-    mbar_init(bar, 1);
-    fence_mbar_init();
-  }
-  if (warp == 0) tmem_alloc<64>(slot);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = *slot;
-
-  const int R = 128 / W, WP = W + 2, RP = R + 2;
-  const int elems = 3 * RP * WP;
-  const int tiles_per_img = H * W / 128;
-  const int tiles = N * tiles_per_img;
-  constexpr uint32_t idesc = umma_idesc_tf32(64, true, true);
-  const uint32_t a_addr = smem_u32(sA), b_addr = smem_u32(sB);
-  const int prow = tid / W, pcol = tid - prow * W;
-  const int kb = tid >> 5, pr = tid & 31;  // my pixel: K block and row inside it
-  uint32_t phase = 0;
-  bool first = true;
-
-  for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-    const int n = tile / tiles_per_img, h0 = (tile - n * tiles_per_img) * R;
-    // dY tile (32 KB, contiguous) -> two MN-major atoms per K block
-    const float4* src = reinterpret_cast<const float4*>(dy + (size_t)tile * 128 * 64);
-#pragma unroll 4
-    for (int idx = tid; idx < 128 * 16; idx += kFcTcThreads) {
-      const int p = idx >> 4, c4 = idx & 15;
-      const int r = p & 31, j = c4 & 7;
-      *reinterpret_cast<float4*>(sB + (p >> 5) * 8192 + (c4 >> 3) * 4096 + r * 128 + ((j ^ ((r & 3) << 1)) << 4)) =
-          __ldcs(src + idx);
-    }
-    for (int e = tid; e < elems; e += kFcTcThreads) {
-      const int ci = e / (RP * WP);
-      const int rem = e - ci * (RP * WP);
-      const int r = rem / WP, c = rem - r * WP;
-      const int hh = h0 - 1 + r, ww = c - 1;
-      float v = 0.f;
-      if (hh >= 0 && hh < H && ww >= 0 && ww < W) v = __ldg(x + ((long long)(n * 3 + ci) * H + hh) * W + ww);
-      patch[e] = v;
-    }
-    __syncthreads();
-    {
-      float v[32];
-#pragma unroll
-      for (int dr = 0; dr < 3; ++dr)
-#pragma unroll
-        for (int ds = 0; ds < 3; ++ds)
-#pragma unroll
-          for (int ci = 0; ci < 3; ++ci) v[(dr * 3 + ds) * 3 + ci] = patch[(ci * RP + prow + dr) * WP + pcol + ds];
-#pragma unroll
-      for (int k = 27; k < 32; ++k) v[k] = 0.f;
-#pragma unroll
-      for (int j = 0; j < 8; ++j)
-        *reinterpret_cast<float4*>(sA + kb * 4096 + pr * 128 + ((j ^ ((pr & 3) << 1)) << 4)) =
-            make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-    }
-    fence_proxy_async();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after();
-#pragma unroll
-      for (int b = 0; b < 4; ++b)
-#pragma unroll
-        for (int ks = 0; ks < 4; ++ks)
-          umma_tf32(tmem, umma_smem_desc(a_addr + b * 4096 + ks * 1024, 4096, 512, 1),
-                    umma_smem_desc(b_addr + b * 8192 + ks * 1024, 4096, 512, 1), idesc,
-                    (!first || b > 0 || ks > 0) ? 1u : 0u);
-      umma_commit(bar);
-    }
-    first = false;
-    __syncwarp();
-    mbar_wait(bar, phase, 710);  // the tensor core is done reading this tile's operands
-    phase ^= 1;
-  }
-  tc_fence_after();
-  if (warp == 0) {  // accumulator rows 0..31 = k, columns = co
-    float* out = partials + (size_t)blockIdx.x * (64 * 27);
-#pragma unroll
-    for (int c0 = 0; c0 < 64; c0 += 32) {
-      float v[32];
-      tmem_ld_32x32(tmem + (uint32_t)c0, v);
-      if (lane < 27) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) out[(c0 + j) * 27 + lane] = v[j];
-      }
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 0) {
-    tc_fence_after();
-    tmem_dealloc<64>(tmem);
-  }
 }
 
 }  // namespace dpb

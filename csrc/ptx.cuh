@@ -34,6 +34,13 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// First 1024-byte aligned address of the dynamic shared memory window.  Written as pointer arithmetic on the
+// __shared__ array (not an integer round trip) so the compiler keeps the address space and emits LDS / STS rather
+// than generic LD / ST for everything derived from it.
+__device__ __forceinline__ uint8_t* smem_align_1024(uint8_t* smem_raw) {
+  return smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+}
+
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile(
