@@ -31,6 +31,8 @@ struct ConvGemmParams {
   int M_total, N_total;  // GEMM extents: fprop/dgrad M = pixels; wgrad M = Cout.  N = channels of the output columns
   int k_iters;           // total K iterations of 32: fprop/dgrad 9*Ck/32; wgrad ceil(pixels/32)
   int splits;            // split-K factor (>=1)
+  int pair_reduce;       // splits == 2 only: the CTA that finishes second adds its partner's partial tile itself and writes
+                         // the final output (a + b == b + a, so the result does not depend on who is second); no reduce kernel
   int box_w, box_h, box_n;  // pixel box of one A tile (fprop/dgrad: 128 pixels) or one K chunk (wgrad: 32 pixels)
   float* out;            // fprop: Y[pix][Cout]; dgrad: dX[pix][Cin]; wgrad: dW[Cout][9][Cin]
   long long out_ld;      // row pitch of `out` in floats
@@ -343,6 +345,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     float4 csum[kSets], csq[kSets];
 #pragma unroll
     for (int s = 0; s < kSets; ++s) csum[s] = csq[s] = make_float4(0.f, 0.f, 0.f, 0.f);
+    bool finalize = p.splits == 1;  // this CTA writes the finished output tile (uniform over the epilogue warps)
+    const float4* partner = nullptr;
     if (p.splits > 1) {
       float4* dst = reinterpret_cast<float4*>(ws + (size_t)(q * 32) * NT);
 #pragma unroll 8
@@ -350,13 +354,37 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         const int idx = it * 32 + lane, row = idx / kChunks, chunk = idx % kChunks;
         dst[idx] = *reinterpret_cast<const float4*>(tile + row * NT + ((chunk ^ (row & 7)) << 2));
       }
-    } else {
+      if (p.pair_reduce) {
+        // two splits: whoever takes the second ticket of this tile finds the partner's partial complete in the workspace
+        // (L2) and finishes the tile from its own slab (still in shared memory) + that partial
+        uint32_t* ticket = tmem_slot + 1;
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (threadIdx.x == 64) {
+          const unsigned old = atomicAdd(&p.counters[tile_id], 1u);
+          if (old == 1u) p.counters[tile_id] = 0u;  // self-resetting for the next launch
+          *ticket = old;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        finalize = *ticket == 1u;
+        if (finalize) {
+          __threadfence();
+          partner = reinterpret_cast<const float4*>(p.workspace + ((size_t)tile_id * 2 + (1 - split)) * (size_t)(128 * NT) +
+                                                    (size_t)(q * 32) * NT);
+        }
+      }
+    }
+    if (finalize) {
       const bool stats = MODE == kFprop && p.stat_sum != nullptr;
       float* obase = p.out + (size_t)row_base * p.out_ld + (size_t)(MODE == kWgrad ? wtap * p.CinW : 0) + n_tile * NT;
 #pragma unroll 8
       for (int it = 0; it < kIters; ++it) {
         const int idx = it * 32 + lane, row = idx / kChunks, chunk = idx % kChunks;
         float4 y = *reinterpret_cast<const float4*>(tile + row * NT + ((chunk ^ (row & 7)) << 2));
+        if (partner != nullptr) {
+          const float4 o = __ldcg(partner + idx);
+          y.x += o.x; y.y += o.y; y.z += o.z; y.w += o.w;
+        }
         if (MODE == kFprop && p.bias != nullptr) {
           const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n_tile * NT) + chunk);
           y.x += b.x; y.y += b.y; y.z += b.z; y.w += b.w;
@@ -399,7 +427,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     // named barrier over the 128 epilogue threads
     asm volatile("bar.sync 1, 128;" ::: "memory");
     const int et = threadIdx.x - 64;  // 0..127
-    if (p.splits == 1) {
+    if (finalize) {
       if (MODE == kFprop && p.stat_sum != nullptr) {
         for (int c = et; c < NT; c += 128) {
           float s0 = 0.f, s1 = 0.f;

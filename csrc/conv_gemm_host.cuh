@@ -104,8 +104,9 @@ int launch_conv_gemm_cl(const CUtensorMap& mA, const CUtensorMap& mB, const Conv
     cfg.numAttrs = 1;
     DPB_CUDA(cudaLaunchKernelEx(&cfg, kern, mA, mB, p));
   }
-  g_conv_last_launches = p.splits > 1 ? 2 : 1;
-  if (p.splits > 1) {
+  const bool reduce_kernel = p.splits > 1 && !p.pair_reduce;
+  g_conv_last_launches = reduce_kernel ? 2 : 1;
+  if (reduce_kernel) {
     const int m_tiles = grid.x, n_tiles = grid.y;
     const int tiles = m_tiles * n_tiles * (MODE == kWgrad ? 9 : 1);
     const int pieces = splitk_pieces(tiles, m_tiles, NT);
@@ -140,8 +141,9 @@ int launch_conv_gemm_pair(const CUtensorMap& mA, const CUtensorMap& mB, const Co
   cfg.attrs = at;
   cfg.numAttrs = 1;
   DPB_CUDA(cudaLaunchKernelEx(&cfg, kern, mA, mB, p));
-  g_conv_last_launches = p.splits > 1 ? 2 : 1;
-  if (p.splits > 1) {
+  const bool reduce_kernel = p.splits > 1 && !p.pair_reduce;
+  g_conv_last_launches = reduce_kernel ? 2 : 1;
+  if (reduce_kernel) {
     const int m_tiles = grid.x, n_tiles = grid.y;
     const int tiles = m_tiles * n_tiles * (MODE == kWgrad ? 9 : 1);
     const int pieces = splitk_pieces(tiles, m_tiles, NT);
@@ -191,6 +193,10 @@ constexpr int kConvCounterSlots = 8192;
 inline int g_tune_target_ctas = 296;
 inline int g_tune_wide_nt = 128;
 inline int g_tune_min_k_iters = 8;  // k-iterations (of 32) a split must keep; fewer, fatter splits = less workspace traffic
+// Two-way splits finished inside the GEMM kernel (ConvGemmParams::pair_reduce).  Off: measured 1.010 vs 0.976 ms/step
+// at batch 256 although it removes 7 launches -- the second CTA's extra fence + 64 KB read + store sit on every
+// tile's critical path, while the separate reduce kernel spreads the same bytes over the whole GPU.
+inline int g_tune_pair_reduce = 0;
 
 inline int pick_splits(int tiles, int k_iters, int nt, int forced) {
   int splits = 1;
@@ -243,6 +249,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
     const int m_tiles = (int)((pixels + 127) / 128);
     const int n_tiles = cn / nt;
     p.splits = pick_splits(m_tiles * n_tiles, p.k_iters, nt, splits_override);
+    p.pair_reduce = (p.splits == 2 && g_tune_pair_reduce && m_tiles * n_tiles <= kConvCounterSlots) ? 1 : 0;
     const int cl = pick_cluster(m_tiles, nt);
     {
       cuuint64_t dims[4] = {(cuuint64_t)ck, (cuuint64_t)g.w, (cuuint64_t)g.h, (cuuint64_t)g.n};
@@ -264,7 +271,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
     }
     grid = dim3(m_tiles, n_tiles, p.splits);
     if (out_m_tiles)  // BatchNorm partial rows written
-      *out_m_tiles = p.splits > 1 ? splitk_pieces(m_tiles * n_tiles, m_tiles, nt) * m_tiles : m_tiles;
+      *out_m_tiles = (p.splits > 1 && !p.pair_reduce) ? splitk_pieces(m_tiles * n_tiles, m_tiles, nt) * m_tiles : m_tiles;
     if (mode == kFprop) return launch_conv_gemm_mode<kFprop>(nt, cl, mA, mB, p, grid, stream);
     return launch_conv_gemm_mode<kDgrad>(nt, cl, mA, mB, p, grid, stream);
   }
@@ -281,6 +288,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
   const int m_tiles = (g.cout + 127) / 128;
   const int n_tiles = g.cin / nt;
   p.splits = pick_splits(m_tiles * n_tiles * 9, p.k_iters, nt, splits_override);
+  p.pair_reduce = (p.splits == 2 && g_tune_pair_reduce && m_tiles * n_tiles * 9 <= kConvCounterSlots) ? 1 : 0;
   {
     cuuint64_t dims[2] = {(cuuint64_t)g.cout, (cuuint64_t)pixels};
     cuuint64_t str[1] = {(cuuint64_t)g.cout * 4};

@@ -10,6 +10,7 @@
 #include "conv_gemm.cuh"
 #include "conv_gemm_host.cuh"
 #include "bn_relu_pool.cuh"
+#include "fused_tail.cuh"
 #include "first_conv.cuh"
 #include "first_conv_tc.cuh"
 #include "first_conv_tc_wgrad.cuh"
@@ -60,6 +61,8 @@ int dpb_set_tuning(int key, int value) {
   if (key == 5 && (value == 1 || value == 2 || value == 4)) { g_tune_cluster = value; return 0; }
   if (key == 6) { g_tune_pair = value ? 1 : 0; return 0; }
   if (key == 7) { g_tune_first_tc = value ? 1 : 0; return 0; }
+  if (key == 8) { g_tune_pair_reduce = value ? 1 : 0; return 0; }
+  if (key == 9 && value >= 0) { g_tune_tail_max_pixels = value; return 0; }
   return set_error(-30, "dpb_set_tuning: bad key/value %d/%d", key, value);
 }
 
@@ -171,11 +174,21 @@ int dpb_bn_relu_pool_fwd(const float* y, const float* scale, const float* shift,
 
 int dpb_bn_bwd_blocks(void) { return kBnBwdBlocks; }
 
+int dpb_bn_bwd_launches(int n, int h, int w, int c, int pool) {
+  return tail_eligible((long long)n * h * w, c, h, w, pool != 0) ? 1 : 3;
+}
+
 int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, const float* shift,
                          const float* save_mean, const float* save_invstd, const float* gamma, float* part,
                          float* coef, float* dgamma, float* dbeta, float* conv_dbias, float* dy, int n, int h, int w,
                          int c, int pool, dpb_stream_t stream) {
   if (c % 4 || c > 1024) return set_error(-2, "bn_relu_pool_bwd: C must be a multiple of 4 and <= 1024 (got %d)", c);
+  if (tail_eligible((long long)n * h * w, c, h, w, pool != 0)) {  // small layer: one cluster kernel, no scratch
+    TailBwdParams tp{y, dout, scale, shift, save_mean, save_invstd, gamma, dy, dgamma, dbeta, conv_dbias, n * h * w, c, h, w};
+    if (pool) DPB_CUDA(launch_tail(tail_bwd_kernel<true>, tp, c, S(stream)));
+    else DPB_CUDA(launch_tail(tail_bwd_kernel<false>, tp, c, S(stream)));
+    return 0;
+  }
   const int c4 = c / 4;
   const long long opix = pool ? (long long)n * (h / 2) * (w / 2) : (long long)n * h * w;
   const int pl = 256 / c4;

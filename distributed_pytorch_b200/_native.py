@@ -86,6 +86,7 @@ _SIGNATURES = {
     "dpb_bn_eval_scale_shift": (c_int, [_I, _P, _P, _P, _P, _F, _P, _P, _P]),
     "dpb_bn_relu_pool_fwd": (c_int, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dpb_bn_bwd_blocks": (c_int, []),
+    "dpb_bn_bwd_launches": (c_int, [_I, _I, _I, _I, _I]),
     "dpb_bn_relu_pool_bwd": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dpb_noalloc_max_channels": (c_int, []),
     "dpb_bn_relu_pool_bwd_noalloc": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
@@ -136,7 +137,7 @@ def load(build_if_missing: bool = True):
                 build()
             lib = ctypes.CDLL(LIB_PATH)
             _bind(lib)
-            for key, env in ((0, "DPB_CONV_TARGET_CTAS"), (1, "DPB_CONV_NT"), (2, "DPB_COMM_BLOCKS"), (3, "DPB_CONV_MIN_K_ITERS"), (4, "DPB_PDL"), (5, "DPB_CONV_CLUSTER"), (6, "DPB_CONV_PAIR"), (7, "DPB_FIRST_TC")):
+            for key, env in ((0, "DPB_CONV_TARGET_CTAS"), (1, "DPB_CONV_NT"), (2, "DPB_COMM_BLOCKS"), (3, "DPB_CONV_MIN_K_ITERS"), (4, "DPB_PDL"), (5, "DPB_CONV_CLUSTER"), (6, "DPB_CONV_PAIR"), (7, "DPB_FIRST_TC"), (8, "DPB_PAIR_REDUCE"), (9, "DPB_TAIL_MAX_PIXELS")):
                 if os.environ.get(env):
                     lib.dpb_set_tuning(key, int(os.environ[env]))
             _lib = lib

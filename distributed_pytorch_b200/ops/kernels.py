@@ -236,7 +236,7 @@ def bn_relu_pool_bwd(y, dout, stats, gamma, dgamma, dbeta, conv_dbias, pool: boo
                                      N.ptr(dgamma), N.ptr(dbeta), N.ptr(conv_dbias), N.ptr(dy), n, h, w, c, int(pool),
                                      N.stream()),
             "dpb_bn_relu_pool_bwd")
-    N.count_launches(3)
+    N.count_launches(lib.dpb_bn_bwd_launches(n, h, w, c, int(pool)))
     return dy
 
 

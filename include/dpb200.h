@@ -68,6 +68,9 @@ int dpb_bn_relu_pool_fwd(const float* y, const float* scale, const float* shift,
 /* Backward of the fused block.  part: scratch [2][dpb_bn_bwd_blocks()][c]; coef: scratch [3][c].
  * conv_dbias (optional): gradient of the preceding conv's bias, exactly zero under training-mode BatchNorm. */
 int dpb_bn_bwd_blocks(void);
+/* Kernels dpb_bn_relu_pool_bwd launches for this shape: 1 when the layer is small enough for the cluster kernel (a
+ * cluster of 8 CTAs per 32 channels exchanges the per-channel sums through distributed shared memory), else 3. */
+int dpb_bn_bwd_launches(int n, int h, int w, int c, int pool);
 int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, const float* shift,
                          const float* save_mean, const float* save_invstd, const float* gamma, float* part,
                          float* coef, float* dgamma, float* dbeta, float* conv_dbias, float* dy, int n, int h, int w,

@@ -68,6 +68,21 @@ def test_conv_all_modes_default_heuristics(K, N, H, Cin, Cout):
     _check(dw.cpu(), dw_ref, "wgrad")
 
 
+@pytest.fixture
+def pair_reduce():
+    """Two-way splits finished inside the GEMM kernel by whichever CTA arrives second (dpb_set_tuning key 8)."""
+    from distributed_pytorch_b200 import _native
+    lib = _native.require()
+    lib.dpb_set_tuning(8, 1)
+    yield
+    lib.dpb_set_tuning(8, 0)
+
+
+@pytest.mark.parametrize("nt", [64, 128, 256])
+def test_conv_two_way_split_in_kernel(K, pair_reduce, nt):
+    test_conv_tiles_and_split_k(K, nt, 2)
+
+
 @pytest.mark.parametrize("nt,splits", [(64, 1), (128, 1), (256, 1), (128, 3), (64, 5), (256, 2)])
 def test_conv_tiles_and_split_k(K, nt, splits):
     N, H, Cin, Cout = 4, 8, 256, 256

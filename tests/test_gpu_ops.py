@@ -60,6 +60,20 @@ def test_linear_and_cross_entropy(K):
         assert torch.allclose(db.cpu(), b.grad, rtol=1e-4, atol=1e-6)
 
 
+@pytest.mark.parametrize("N,C,H,pool", [(4, 64, 32, True), (8, 128, 16, True), (32, 512, 2, True), (8, 512, 4, False)])
+def test_bn_backward_cluster_kernel(K, N, C, H, pool):
+    """Same oracle through the one-launch cluster kernel (DSMEM exchange of the per-channel sums), enabled here for
+    layers of up to 8192 pixels (it is off by default)."""
+    from distributed_pytorch_b200 import _native
+    lib = _native.require()
+    lib.dpb_set_tuning(9, 8192)
+    try:
+        assert lib.dpb_bn_bwd_launches(N, H, H, C, int(pool)) == (1 if N * H * H <= 8192 else 3)
+        test_bn_relu_pool_forward_backward(K, N, C, H, pool)
+    finally:
+        lib.dpb_set_tuning(9, 0)
+
+
 @pytest.mark.parametrize("N,C,H,pool", [(4, 64, 32, True), (3, 128, 16, True), (5, 256, 8, False), (32, 512, 2, True),
                                         (7, 512, 4, False)])
 def test_bn_relu_pool_forward_backward(K, N, C, H, pool):
