@@ -40,6 +40,8 @@ def parse_args(argv=None):
     p.add_argument("--global-batch", type=int, default=GLOBAL_BATCH)
     p.add_argument("--per-rank-batch", type=int, default=None,
                    help="weak scaling: fixed per-rank batch (the reference's own convention is 256 per rank)")
+    p.add_argument("--bucket-cap-mb", type=float, default=None,
+                   help="ddp mode: gradient bucket size (default: the framework's, see DistributedDataParallel)")
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--no-fuse-optimizer", action="store_true")
     p.add_argument("--all-modes", action="store_true", help="also time the other sync modes (extra keys)")
@@ -228,7 +230,8 @@ def build_ours(mode: str, rank: int, world: int, args):
     dev = torch.device("cuda", torch.cuda.current_device())
     model = dpb.VGG11().to(dev)
     if mode == "ddp":
-        model = dpb.DistributedDataParallel(model)
+        kw = {} if args.bucket_cap_mb is None else {"bucket_cap_mb": args.bucket_cap_mb}
+        model = dpb.DistributedDataParallel(model, **kw)
     opt = dpb.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
     if mode == "gather":
         sync = dpb.GatherScatterSync(model, world, rank)
