@@ -9,8 +9,10 @@ import subprocess
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "distributed_pytorch_b200", "_lib", "libdpb200.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-FULL = {"conv_gemm_kernel<0, 128, 3, 1>": "conv_gemm_fprop_nt128.sass",
-        "conv_gemm_kernel<2, 128, 3, 1>": "conv_gemm_wgrad_nt128.sass",
+FULL = {"conv_gemm_kernel<0, 128, 3, 1, 1>": "conv_gemm_fprop_nt128.sass",
+        "conv_gemm_kernel<2, 128, 3, 1, 1>": "conv_gemm_wgrad_nt128.sass",
+        "first_conv_fprop_tc_kernel": "first_conv_fprop_tc.sass",
+        "first_conv_wgrad_tc_kernel": "first_conv_wgrad_tc.sass",
         "allreduce_twoshot_kernel<false, 8, 2>": "allreduce_twoshot_8ranks.sass"}
 
 
