@@ -41,9 +41,18 @@ size_t dpb_conv_counter_bytes(void);
 int dpb_conv3x3_gemm(int mode, int n, int h, int w, int cin, int cout, const float* in, const float* in2,
                      const float* weight, float* out, const float* bias, float* stat_sum, float* stat_sq,
                      void* workspace, void* counters, int nt, int splits, int* m_tiles_out, dpb_stream_t stream);
-/* Heuristic knobs of the tensor-core conv. key 0: CTA count split-K aims for (default 296); key 1: preferred N tile
- * (64 / 128 / 256, default 128) when it divides the GEMM N extent; key 2: default grid cap of the collective kernels
- * (default 64, at most 128). */
+/* Heuristic knobs (the Python loader also reads them from the environment variable in brackets).
+ *  0 [DPB_CONV_TARGET_CTAS]  CTA count the split-K heuristic aims for (default 296 = two per SM)
+ *  1 [DPB_CONV_NT]           preferred N tile (64 / 128 / 256, default 128) when it divides the GEMM N extent
+ *  2 [DPB_COMM_BLOCKS]       default grid cap of the collective kernels (default 64, at most 128)
+ *  3 [DPB_CONV_MIN_K_ITERS]  K iterations (of 32) a split must keep (default 8)
+ *  4 [DPB_PDL]               programmatic dependent launch on every compute kernel (default 0)
+ *  5 [DPB_CONV_CLUSTER]      TMA multicast of the B tile over a 1 / 2 / 4-CTA cluster (default 1 = none)
+ *  6 [DPB_CONV_PAIR]         cta_group::2 CTA pairs, M = 256 MMAs (default 0)
+ *  7 [DPB_FIRST_TC]          first (Cin = 3) layer on the tensor cores when the image tiles into 128 pixels (default 1)
+ *  8 [DPB_PAIR_REDUCE]       finish two-way split-K inside the GEMM kernel instead of the reduce kernel (default 0)
+ *  9 [DPB_TAIL_MAX_PIXELS]   BatchNorm backward as one cluster kernel for layers up to this many pixels (default 0 = off)
+ * Defaults are the measured optimum on B200; returns non-zero for an unknown key / bad value. */
 int dpb_set_tuning(int key, int value);
 /* Kernels launched by the calling thread's most recent dpb_conv3x3_gemm (1, or 2 when split-K adds its reduce). */
 int dpb_conv_last_launches(void);

@@ -36,7 +36,9 @@ def bench_table():
         return
     rows.sort(key=lambda r: (r[1], r[0]))
     with open(os.path.join(PROF, "bench_multi_gpu.md"), "w") as fh:
-        fh.write("# bench.py, ours vs the unmodified reference (`--impl reference`), same box, global batch 256\n\n"
+        fh.write("# bench.py, ours vs the unmodified reference (`--impl reference`), global batch 256\n\n"
+                 "Our rows are the latest run of each configuration; the reference rows were taken earlier in the round on a box of\n"
+                 "the same type (8 x B200, same image) -- the reference code did not change.  1-GPU: see the README / DESIGN table.\n"
                  "Device-timed (CUDA events, max over ranks), 30 steps after 5 warm-ups; `e2e` adds the pinned-host -> device\n"
                  "copy of every batch and a `loss.item()` per step.  Raw JSON lines: `profiles/raw/`.\n\n"
                  "| mode | GPUs | ours ms/step | ours img/s | ours e2e img/s | ref ms/step | ref img/s | ref e2e img/s | speed-up (e2e) | clocks (MHz, reasons) |\n"
