@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <mutex>
 #include "conv_gemm.cuh"
+#include "conv_gemm_persistent.cuh"
 #include "splitk_reduce.cuh"
 #include "errors.cuh"
 
@@ -152,9 +153,47 @@ int launch_conv_gemm_pair(const CUtensorMap& mA, const CUtensorMap& mB, const Co
   return 0;
 }
 
+// Persistent variant (conv_gemm_persistent.cuh): one CTA per SM walks the work units the plain kernel would launch as
+// CTAs.  cl == kPersistMode selects it.
+constexpr int kPersistMode = -3;
+inline int device_sm_count() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+      sms = 148;
+  }
+  return sms;
+}
+template <int MODE, int NT>
+int launch_conv_gemm_persistent(const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
+                                cudaStream_t stream) {
+  constexpr int STAGES = (NT == 256) ? 4 : 6;  // NT 128: 6 x 32 KB, NT 64: 6 x 24 KB, NT 256: 4 x 48 KB
+  using S = ConvPersistSmem<NT, STAGES>;
+  auto kern = conv_gemm_persistent_kernel<MODE, NT, STAGES>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DPB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+    attr_set = true;
+  }
+  const int units = (int)(grid.x * grid.y * grid.z);
+  const int ctas = units < device_sm_count() ? units : device_sm_count();
+  DPB_CUDA(launch_k(kern, dim3(ctas), dim3(192), S::kTotal, stream, mA, mB, p, (int)grid.x, (int)grid.y, units));
+  const bool reduce_kernel = p.splits > 1;
+  g_conv_last_launches = reduce_kernel ? 2 : 1;
+  if (reduce_kernel) {
+    const int m_tiles = grid.x, n_tiles = grid.y;
+    const int tiles = m_tiles * n_tiles * (MODE == kWgrad ? 9 : 1);
+    const int pieces = splitk_pieces(tiles, m_tiles, NT);
+    DPB_CUDA(launch_k(splitk_reduce_kernel<MODE>, dim3(tiles, pieces), dim3(256), 0, stream, p, NT, m_tiles, n_tiles, pieces));
+  }
+  return 0;
+}
+
 template <int MODE, int NT>
 int launch_conv_gemm_nt(int cl, const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
                         cudaStream_t stream) {
+  if (cl == kPersistMode) return launch_conv_gemm_persistent<MODE, NT>(mA, mB, p, grid, stream);
   if (cl == kPairMode) return launch_conv_gemm_pair<MODE, NT>(mA, mB, p, grid, stream);
   if (cl == 2) return launch_conv_gemm_cl<MODE, NT, 2>(mA, mB, p, grid, stream);
   if constexpr (NT >= 128) {
@@ -178,7 +217,9 @@ int launch_conv_gemm_mode(int nt, int cl, const CUtensorMap& mA, const CUtensorM
 // g_tune_pair: use CTA pairs (cta_group::2) whenever the M tiles come in twos; returns kPairMode then.
 inline int g_tune_cluster = 1;
 inline int g_tune_pair = 0;
-inline int pick_cluster(int m_tiles, int nt) {
+inline int g_tune_persistent = 0;  // bit 0: fprop, bit 1: dgrad, bit 2: wgrad run the persistent kernel
+inline int pick_cluster(int m_tiles, int nt, int mode = 0) {
+  if ((g_tune_persistent >> mode) & 1) return kPersistMode;
   if (g_tune_pair && m_tiles % 2 == 0 && (nt / 32) % 2 == 0) return kPairMode;
   int cl = g_tune_cluster;
   while (cl > 1 && (m_tiles % cl != 0 || (nt / 32) % cl != 0)) cl >>= 1;
@@ -250,7 +291,8 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
     const int n_tiles = cn / nt;
     p.splits = pick_splits(m_tiles * n_tiles, p.k_iters, nt, splits_override);
     p.pair_reduce = (p.splits == 2 && g_tune_pair_reduce && m_tiles * n_tiles <= kConvCounterSlots) ? 1 : 0;
-    const int cl = pick_cluster(m_tiles, nt);
+    const int cl = pick_cluster(m_tiles, nt, mode);
+    if (cl == kPersistMode) p.pair_reduce = 0;  // the persistent kernel always leaves split-K to the reduce kernel
     {
       cuuint64_t dims[4] = {(cuuint64_t)ck, (cuuint64_t)g.w, (cuuint64_t)g.h, (cuuint64_t)g.n};
       cuuint64_t str[3] = {(cuuint64_t)ck * 4, (cuuint64_t)g.w * ck * 4, (cuuint64_t)g.h * g.w * ck * 4};
@@ -261,7 +303,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
       cuuint64_t dims[2] = {(cuuint64_t)9 * g.cin, (cuuint64_t)g.cout};
       cuuint64_t str[1] = {(cuuint64_t)9 * g.cin * 4};
       // each CTA of a multicast cluster fetches nt/cl rows; each CTA of a pair stages nt/2 rows
-      cuuint32_t box[2] = {32, (cuuint32_t)(cl == kPairMode ? nt / 2 : nt / cl)};
+      cuuint32_t box[2] = {32, (cuuint32_t)(cl == kPairMode ? nt / 2 : (cl > 1 ? nt / cl : nt))};
       if ((rc = make_map_f32(&mB, w, 2, dims, str, box))) return rc;
     } else {
       cuuint64_t dims[2] = {(cuuint64_t)9 * g.cin, (cuuint64_t)g.cout};
@@ -303,7 +345,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
   }
   grid = dim3(m_tiles, n_tiles, 9 * p.splits);
   if (out_m_tiles) *out_m_tiles = m_tiles;
-  return launch_conv_gemm_mode<kWgrad>(nt, pick_cluster(m_tiles, nt), mA, mB, p, grid, stream);
+  return launch_conv_gemm_mode<kWgrad>(nt, pick_cluster(m_tiles, nt, kWgrad), mA, mB, p, grid, stream);
 }
 
 }  // namespace dpb

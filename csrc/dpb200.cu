@@ -63,6 +63,7 @@ int dpb_set_tuning(int key, int value) {
   if (key == 7) { g_tune_first_tc = value ? 1 : 0; return 0; }
   if (key == 8) { g_tune_pair_reduce = value ? 1 : 0; return 0; }
   if (key == 9 && value >= 0) { g_tune_tail_max_pixels = value; return 0; }
+  if (key == 10 && value >= 0 && value <= 7) { g_tune_persistent = value; return 0; }
   return set_error(-30, "dpb_set_tuning: bad key/value %d/%d", key, value);
 }
 

@@ -83,6 +83,27 @@ def test_conv_two_way_split_in_kernel(K, pair_reduce, nt):
     test_conv_tiles_and_split_k(K, nt, 2)
 
 
+@pytest.fixture
+def persistent():
+    """All three GEMMs through the persistent kernel (one CTA per SM, TMEM double-buffered; dpb_set_tuning key 10)."""
+    from distributed_pytorch_b200 import _native
+    lib = _native.require()
+    lib.dpb_set_tuning(10, 7)
+    yield
+    lib.dpb_set_tuning(10, 0)
+
+
+@pytest.mark.parametrize("nt,splits", [(64, 1), (128, 1), (256, 1), (128, 3), (64, 5), (128, 0)])
+def test_conv_persistent_tiles_and_split_k(K, persistent, nt, splits):
+    test_conv_tiles_and_split_k(K, nt, splits)
+
+
+@pytest.mark.parametrize("N,H,Cin,Cout", [(32, 16, 64, 128), (16, 8, 128, 256), (64, 4, 256, 512), (256, 2, 512, 512)])
+def test_conv_persistent_layer_shapes(K, persistent, N, H, Cin, Cout):
+    """VGG layer shapes: several work units per CTA, so the accumulator ping-pong and the cross-unit stage ring run."""
+    test_conv_all_modes_default_heuristics(K, N, H, Cin, Cout)
+
+
 @pytest.mark.parametrize("nt,splits", [(64, 1), (128, 1), (256, 1), (128, 3), (64, 5), (256, 2)])
 def test_conv_tiles_and_split_k(K, nt, splits):
     N, H, Cin, Cout = 4, 8, 256, 256

@@ -45,6 +45,22 @@ for h, cin, cout in layers:
         wait, loop, kc, acc_wait, epi, setup, cyc_total, ns_total = d
         tr = dump[12800:12800 + 3072].view(torch.int32).cpu().view(-1, 3).long() & 0xFFFFFFFF
         tr = tr[tr[:, 0] != 0]
+        if len(tr) == 0:  # persistent kernel (DPB_CONV_PERSIST): no per-CTA trace, but two more counters
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for _ in range(20):
+                    K.conv3x3_gemm(*args)
+            g.replay()
+            torch.cuda.synchronize()
+            s.record()
+            for _ in range(5):
+                g.replay()
+            e.record()
+            torch.cuda.synchronize()
+            print(f"{h:2d}x{h:<2d} {cin:3d}->{cout:3d} {name}: in-graph {s.elapsed_time(e) * 1e3 / 100:6.1f} us/launch | persistent, {cyc_total:.0f} units/CTA, "
+                  f"{int(kc)} k-iters: issue loop {loop:8.0f} cyc ({loop / max(kc, 1):5.0f}/iter), waiting for operands {100 * wait / max(loop, 1):4.1f}%, "
+                  f"for a free accumulator {100 * setup / max(loop, 1):4.1f}% | epilogue warps: waited {acc_wait:7.0f}, drained {epi:7.0f} cyc")
+            continue
         t0 = int(tr[:, 0].min())
         st, en = (tr[:, 0] - t0) & 0xFFFFFFFF, (tr[:, 1] - t0) & 0xFFFFFFFF
         life = (en - st).float()
