@@ -11,6 +11,7 @@
 #include "conv_gemm_host.cuh"
 #include "bn_relu_pool.cuh"
 #include "fused_tail.cuh"
+#include "standalone_ops.cuh"
 #include "first_conv.cuh"
 #include "first_conv_tc.cuh"
 #include "first_conv_tc_wgrad.cuh"
@@ -212,6 +213,80 @@ int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, 
   } else {
     DPB_CUDA(launch_k(bn_bwd_apply_kernel<false>, dim3(ablocks), dim3(256), 0, S(stream), y, dout, scale, shift, coef, dy, units, c, h, w));
   }
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ lone layers
+// The reference's layer types outside the conv->bn->relu[->pool] pattern (standalone_ops.cuh).
+int dpb_relu_fwd(const float* x, float* y, long long n, dpb_stream_t stream) {
+  if (n % 4) return set_error(-40, "relu: element count must be a multiple of 4 (got %lld)", n);
+  DPB_CUDA(launch_k(relu_fwd_kernel, dim3(grid_for(n / 4, 256, 148 * 16)), dim3(256), 0, S(stream), (const float4*)x, (float4*)y, n / 4));
+  return 0;
+}
+
+int dpb_relu_bwd(const float* y, const float* dout, float* dx, long long n, dpb_stream_t stream) {
+  if (n % 4) return set_error(-40, "relu: element count must be a multiple of 4 (got %lld)", n);
+  DPB_CUDA(launch_k(relu_bwd_kernel, dim3(grid_for(n / 4, 256, 148 * 16)), dim3(256), 0, S(stream), (const float4*)y, (const float4*)dout, (float4*)dx, n / 4));
+  return 0;
+}
+
+int dpb_maxpool2x2_fwd(const float* x, float* out, int n, int h, int w, int c, dpb_stream_t stream) {
+  if (c % 4 || ((h | w) & 1)) return set_error(-41, "maxpool2x2: needs C %% 4 == 0 and even H, W (got C=%d, %dx%d)", c, h, w);
+  const long long units = (long long)n * (h / 2) * (w / 2) * (c / 4);
+  DPB_CUDA(launch_k(maxpool2x2_fwd_kernel, dim3(grid_for(units, 256, 148 * 16)), dim3(256), 0, S(stream), (const float4*)x, (float4*)out, units, c / 4, h, w));
+  return 0;
+}
+
+int dpb_maxpool2x2_bwd(const float* x, const float* dout, float* dx, int n, int h, int w, int c, dpb_stream_t stream) {
+  if (c % 4 || ((h | w) & 1)) return set_error(-41, "maxpool2x2: needs C %% 4 == 0 and even H, W (got C=%d, %dx%d)", c, h, w);
+  const long long units = (long long)n * (h / 2) * (w / 2) * (c / 4);
+  DPB_CUDA(launch_k(maxpool2x2_bwd_kernel, dim3(grid_for(units, 256, 148 * 16)), dim3(256), 0, S(stream), (const float4*)x, (const float4*)dout, (float4*)dx, units, c / 4, h, w));
+  return 0;
+}
+
+int dpb_column_stats_blocks(void) { return kColStatBlocks; }
+
+static int column_stat_grid(long long m, int c) {
+  const int pl = 256 / (c / 4);
+  long long b = (m + pl - 1) / pl;
+  return (int)(b < kColStatBlocks ? (b < 1 ? 1 : b) : kColStatBlocks);
+}
+
+int dpb_column_stats(const float* x, float* part_sum, float* part_sq, long long m, int c, int* blocks_out,
+                     dpb_stream_t stream) {
+  if (c % 4 || c > 1024 || c <= 0) return set_error(-42, "column stats: C must be a multiple of 4 and <= 1024 (got %d)", c);
+  const int blocks = column_stat_grid(m, c);
+  DPB_CUDA(launch_k(column_stats_kernel, dim3(blocks), dim3(256), 0, S(stream), (const float4*)x, part_sum, part_sq, m, c / 4));
+  if (blocks_out) *blocks_out = blocks;
+  return 0;
+}
+
+int dpb_column_sum(const float* x, float* part, float* out, long long m, int c, dpb_stream_t stream) {
+  int blocks = 0;
+  if (int rc = dpb_column_stats(x, part, nullptr, m, c, &blocks, stream)) return rc;
+  DPB_CUDA(launch_k(column_reduce_kernel, dim3((c + 31) / 32), dim3(32, 8), 0, S(stream), (const float*)part, blocks, c, out));
+  return 0;
+}
+
+int dpb_bn_apply(const float* x, const float* scale, const float* shift, float* y, long long m, int c,
+                 dpb_stream_t stream) {
+  if (c % 4) return set_error(-43, "bn apply: C must be a multiple of 4 (got %d)", c);
+  const long long n4 = m * (c / 4);
+  DPB_CUDA(launch_k(bn_apply_kernel, dim3(grid_for(n4, 256, 148 * 16)), dim3(256), 0, S(stream), (const float4*)x, scale, shift, (float4*)y, n4, c / 4));
+  return 0;
+}
+
+int dpb_bn_plain_bwd(const float* x, const float* dout, const float* save_mean, const float* save_invstd,
+                     const float* gamma, float* part, float* coef, float* dgamma, float* dbeta, float* dx, long long m,
+                     int c, dpb_stream_t stream) {
+  if (c % 4 || c > 1024 || c <= 0) return set_error(-43, "bn backward: C must be a multiple of 4 and <= 1024 (got %d)", c);
+  const int blocks = column_stat_grid(m, c);
+  float* part_g = part;
+  float* part_gx = part + (size_t)kColStatBlocks * c;
+  DPB_CUDA(launch_k(bn_plain_bwd_reduce_kernel, dim3(blocks), dim3(256), 0, S(stream), (const float4*)x, (const float4*)dout, save_mean, save_invstd, part_g, part_gx, m, c / 4));
+  DPB_CUDA(launch_k(bn_bwd_finalize_kernel, dim3((c + kFinCh - 1) / kFinCh), dim3(kFinCh, kFinRows), 0, S(stream), (const float*)part_g, (const float*)part_gx, blocks, c, (double)m, gamma, save_mean, save_invstd, dgamma, dbeta, (float*)nullptr, coef));
+  const long long n4 = m * (c / 4);
+  DPB_CUDA(launch_k(bn_plain_bwd_apply_kernel, dim3(grid_for(n4, 256, 148 * 16)), dim3(256), 0, S(stream), (const float4*)x, (const float4*)dout, (const float*)coef, (float4*)dx, n4, c));
   return 0;
 }
 

@@ -88,6 +88,15 @@ _SIGNATURES = {
     "dpb_bn_bwd_blocks": (c_int, []),
     "dpb_bn_bwd_launches": (c_int, [_I, _I, _I, _I, _I]),
     "dpb_bn_relu_pool_bwd": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dpb_relu_fwd": (c_int, [_P, _P, _LL, _P]),
+    "dpb_relu_bwd": (c_int, [_P, _P, _P, _LL, _P]),
+    "dpb_maxpool2x2_fwd": (c_int, [_P, _P, _I, _I, _I, _I, _P]),
+    "dpb_maxpool2x2_bwd": (c_int, [_P, _P, _P, _I, _I, _I, _I, _P]),
+    "dpb_column_stats_blocks": (c_int, []),
+    "dpb_column_stats": (c_int, [_P, _P, _P, _LL, _I, POINTER(c_int), _P]),
+    "dpb_column_sum": (c_int, [_P, _P, _P, _LL, _I, _P]),
+    "dpb_bn_apply": (c_int, [_P, _P, _P, _P, _LL, _I, _P]),
+    "dpb_bn_plain_bwd": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _LL, _I, _P]),
     "dpb_noalloc_max_channels": (c_int, []),
     "dpb_bn_relu_pool_bwd_noalloc": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dpb_linear_fwd": (c_int, [_P, _P, _P, _P, _I, _I, _I, _P]),

@@ -28,12 +28,6 @@ CONFIGS = {
 }
 
 
-def _standalone_cuda_error(name: str):
-    return NotImplementedError(
-        f"{name} has no standalone CUDA kernel: on B200 it only exists fused inside the conv->bn->relu[->pool] block. "
-        "Put it in a FusedSequential in that pattern.")
-
-
 class Conv3x3(nn.Conv2d):
     """3x3, stride 1, padding 1, bias (reference model.py:18-23). Weight memory is KRSC."""
 
@@ -48,23 +42,23 @@ class Conv3x3(nn.Conv2d):
         return out
 
     def forward(self, x):
-        if x.is_cuda:
-            raise _standalone_cuda_error("Conv3x3")
-        return super().forward(x)
+        # on its own (not as the head of a conv->bn->relu[->pool] run of a FusedSequential): tcgen05 conv + bias
+        return Fn.conv3x3(x, self.weight, self.bias)
 
 
 class BatchNorm(nn.BatchNorm2d):
     def forward(self, x):
-        if x.is_cuda:
-            raise _standalone_cuda_error("BatchNorm")
-        return super().forward(x)
+        if not x.is_cuda:
+            return super().forward(x)
+        training = self.training or self.running_mean is None
+        momentum = 0.1 if self.momentum is None else self.momentum
+        return Fn.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var,
+                             self.num_batches_tracked if training else None, training, momentum, self.eps)
 
 
 class ReLU(nn.ReLU):
     def forward(self, x):
-        if x.is_cuda:
-            raise _standalone_cuda_error("ReLU")
-        return super().forward(x)
+        return Fn.relu(x) if x.is_cuda else super().forward(x)
 
 
 class MaxPool2x2(nn.MaxPool2d):
@@ -72,9 +66,7 @@ class MaxPool2x2(nn.MaxPool2d):
         super().__init__(kernel_size=2, stride=2)
 
     def forward(self, x):
-        if x.is_cuda:
-            raise _standalone_cuda_error("MaxPool2x2")
-        return super().forward(x)
+        return Fn.max_pool2x2(x) if x.is_cuda else super().forward(x)
 
 
 class Linear(nn.Linear):

@@ -22,7 +22,8 @@ import torch.nn.functional as F
 
 from . import kernels as K
 
-__all__ = ["conv_bn_relu_pool", "linear", "cross_entropy", "grad_destination"]
+__all__ = ["conv_bn_relu_pool", "conv3x3", "batch_norm", "relu", "max_pool2x2", "linear", "cross_entropy",
+           "grad_destination"]
 
 
 def grad_destination(param: torch.Tensor) -> torch.Tensor:
@@ -134,6 +135,152 @@ def conv_bn_relu_pool(x, conv_w, conv_b, bn_w, bn_b, running_mean, running_var, 
     if pool:
         y = F.max_pool2d(y, 2, 2)
     return y
+
+
+# ---- the same layer types on their own (reference model.py:16-25 in any other arrangement) ----------------------------
+class _Conv3x3(torch.autograd.Function):
+    """Conv2d(3x3, stride 1, padding 1, bias) not followed by BatchNorm: tcgen05 fprop / dgrad / wgrad, bias gradient by a
+    fixed-order column sum."""
+
+    @staticmethod
+    def forward(ctx, x, conv_w, conv_b):
+        n, cin, h, w = x.shape
+        cout = conv_w.shape[0]
+        first = cin == 3
+        wk = _as_krsc(conv_w.detach())
+        y = K.nhwc_empty(n, cout, h, w, x.device)
+        if first:
+            if cout != 64:
+                raise NotImplementedError("the Cin=3 entry layer kernel is built for 64 output channels")
+            xin = x.detach().contiguous()
+            K.first_conv_fprop(xin, wk, conv_b, y, False)
+        else:
+            xin = _as_nhwc(x.detach())
+            K.conv3x3_gemm(0, n, h, w, cin, cout, xin, None, wk, y, conv_b, want_stats=False)
+        ctx.first = first
+        ctx.params = (conv_w, conv_b)
+        ctx.save_for_backward(xin, wk)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        xin, wk = ctx.saved_tensors
+        conv_w, conv_b = ctx.params
+        dy = _as_nhwc(dy)
+        n, cout, h, w = dy.shape
+        cin = conv_w.shape[1]
+        d_w = grad_destination(conv_w)
+        if not K.is_nhwc(d_w):
+            raise RuntimeError("conv weight gradients must be KRSC (channels_last) in memory")
+        d_b = None
+        if conv_b is not None:
+            d_b = grad_destination(conv_b)
+            K.column_sum(dy, d_b)
+        dx = None
+        if ctx.first:
+            if ctx.needs_input_grad[0]:
+                raise NotImplementedError("no data-gradient kernel for the Cin=3 entry layer (the network input)")
+            K.first_conv_wgrad(xin, dy, d_w)
+        else:
+            K.conv3x3_gemm(2, n, h, w, cin, cout, dy, xin, wk, d_w)
+            if ctx.needs_input_grad[0]:
+                dx = K.nhwc_empty(n, cin, h, w, dy.device)
+                K.conv3x3_gemm(1, n, h, w, cin, cout, dy, None, wk, dx)
+        return dx, d_w, d_b
+
+
+class _BatchNorm(torch.autograd.Function):
+    """BatchNorm2d on its own: batch statistics by a fixed-order column reduction, then y = x * scale + shift."""
+
+    @staticmethod
+    def forward(ctx, x, bn_w, bn_b, running_mean, running_var, nbt, training, momentum, eps):
+        xin = _as_nhwc(x.detach())
+        n, c, h, w = xin.shape
+        if training:
+            ps, pq, rows = K.column_stats(xin)
+            stats = K.bn_finalize(ps, pq, rows, c, float(n * h * w), bn_w, bn_b, running_mean, running_var, nbt,
+                                  momentum, eps)
+        else:
+            stats = K.bn_eval_scale_shift(c, bn_w, bn_b, running_mean, running_var, eps)
+        y = K.bn_apply(xin, stats[0], stats[1])
+        ctx.training = training
+        ctx.params = (bn_w, bn_b)
+        ctx.save_for_backward(xin, stats)
+        return y
+
+    @staticmethod
+    def backward(ctx, dout):
+        if not ctx.training:
+            raise RuntimeError("backward through an eval-mode BatchNorm is not supported")
+        xin, stats = ctx.saved_tensors
+        bn_w, bn_b = ctx.params
+        d_w, d_b = grad_destination(bn_w), grad_destination(bn_b)
+        dx = K.bn_plain_bwd(xin, _as_nhwc(dout), stats, bn_w, d_w, d_b)
+        return dx, d_w, d_b, None, None, None, None, None, None
+
+
+class _ReLU(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        xin = x.detach()
+        if not (xin.is_contiguous() or K.is_nhwc(xin)):
+            xin = xin.contiguous()
+        y = K.relu_fwd(xin)
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dout):
+        (y,) = ctx.saved_tensors
+        if dout.stride() != y.stride():
+            dout = dout.contiguous(memory_format=torch.channels_last) if K.is_nhwc(y) else dout.contiguous()
+        return K.relu_bwd(y, dout)
+
+
+class _MaxPool2x2(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        xin = _as_nhwc(x.detach())
+        ctx.save_for_backward(xin)
+        return K.maxpool2x2_fwd(xin)
+
+    @staticmethod
+    def backward(ctx, dout):
+        (xin,) = ctx.saved_tensors
+        return K.maxpool2x2_bwd(xin, _as_nhwc(dout))
+
+
+def conv3x3(x, conv_w, conv_b):
+    """Conv2d(3x3, s1, p1) alone (reference model.py:18-23)."""
+    if x.is_cuda:
+        return _Conv3x3.apply(x, conv_w, conv_b)
+    return F.conv2d(x, conv_w, conv_b, stride=1, padding=1)
+
+
+def batch_norm(x, bn_w, bn_b, running_mean, running_var, num_batches_tracked, training: bool, momentum: float = 0.1,
+               eps: float = 1e-5):
+    """BatchNorm2d alone (reference model.py:24)."""
+    if x.is_cuda:
+        return _BatchNorm.apply(x, bn_w, bn_b, running_mean, running_var, num_batches_tracked, training, momentum, eps)
+    if training and num_batches_tracked is not None:
+        num_batches_tracked += 1
+    return F.batch_norm(x, running_mean, running_var, bn_w, bn_b, training, momentum, eps)
+
+
+def relu(x):
+    """ReLU alone (reference model.py:25)."""
+    if x.is_cuda:
+        if x.numel() % 4:
+            raise NotImplementedError("the CUDA ReLU kernel works on multiples of 4 elements")
+        return _ReLU.apply(x)
+    return F.relu(x)
+
+
+def max_pool2x2(x):
+    """MaxPool2d(2, 2) alone (reference model.py:16)."""
+    if x.is_cuda:
+        return _MaxPool2x2.apply(x)
+    return F.max_pool2d(x, 2, 2)
 
 
 class _Linear(torch.autograd.Function):

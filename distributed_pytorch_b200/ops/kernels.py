@@ -240,6 +240,86 @@ def bn_relu_pool_bwd(y, dout, stats, gamma, dgamma, dbeta, conv_dbias, pool: boo
     return dy
 
 
+# ---- the reference's layer types on their own (anything that is not conv -> bn -> relu [-> pool]) ----------------------
+def relu_fwd(x: torch.Tensor) -> torch.Tensor:
+    lib = N.require()
+    y = torch.empty_like(x)
+    N.check(lib.dpb_relu_fwd(N.ptr(x), N.ptr(y), x.numel(), N.stream()), "dpb_relu_fwd")
+    N.count_launches(1)
+    return y
+
+
+def relu_bwd(y: torch.Tensor, dout: torch.Tensor) -> torch.Tensor:
+    lib = N.require()
+    dx = torch.empty_like(y)
+    N.check(lib.dpb_relu_bwd(N.ptr(y), N.ptr(dout), N.ptr(dx), y.numel(), N.stream()), "dpb_relu_bwd")
+    N.count_launches(1)
+    return dx
+
+
+def maxpool2x2_fwd(x: torch.Tensor) -> torch.Tensor:
+    lib = N.require()
+    n, c, h, w = x.shape
+    out = nhwc_empty(n, c, h // 2, w // 2, x.device)
+    N.check(lib.dpb_maxpool2x2_fwd(N.ptr(x), N.ptr(out), n, h, w, c, N.stream()), "dpb_maxpool2x2_fwd")
+    N.count_launches(1)
+    return out
+
+
+def maxpool2x2_bwd(x: torch.Tensor, dout: torch.Tensor) -> torch.Tensor:
+    lib = N.require()
+    n, c, h, w = x.shape
+    dx = torch.empty_like(x)
+    N.check(lib.dpb_maxpool2x2_bwd(N.ptr(x), N.ptr(dout), N.ptr(dx), n, h, w, c, N.stream()), "dpb_maxpool2x2_bwd")
+    N.count_launches(1)
+    return dx
+
+
+def column_stats(x: torch.Tensor):
+    """Per-block partial sums / sums of squares over the pixels of an NHWC tensor: (part_sum, part_sq, rows)."""
+    lib = N.require()
+    n, c, h, w = x.shape
+    blocks = lib.dpb_column_stats_blocks()
+    ps = torch.empty((blocks, c), device=x.device, dtype=torch.float32)
+    pq = torch.empty((blocks, c), device=x.device, dtype=torch.float32)
+    rows = ctypes.c_int(0)
+    N.check(lib.dpb_column_stats(N.ptr(x), N.ptr(ps), N.ptr(pq), n * h * w, c, ctypes.byref(rows), N.stream()),
+            "dpb_column_stats")
+    N.count_launches(1)
+    return ps, pq, rows.value
+
+
+def column_sum(x: torch.Tensor, out: torch.Tensor) -> None:
+    """out[c] = sum over pixels of an NHWC tensor (bias gradient of a conv that is not followed by BatchNorm)."""
+    lib = N.require()
+    n, c, h, w = x.shape
+    part = torch.empty((lib.dpb_column_stats_blocks(), c), device=x.device, dtype=torch.float32)
+    N.check(lib.dpb_column_sum(N.ptr(x), N.ptr(part), N.ptr(out), n * h * w, c, N.stream()), "dpb_column_sum")
+    N.count_launches(2)
+
+
+def bn_apply(x: torch.Tensor, scale, shift) -> torch.Tensor:
+    lib = N.require()
+    n, c, h, w = x.shape
+    y = torch.empty_like(x)
+    N.check(lib.dpb_bn_apply(N.ptr(x), N.ptr(scale), N.ptr(shift), N.ptr(y), n * h * w, c, N.stream()), "dpb_bn_apply")
+    N.count_launches(1)
+    return y
+
+
+def bn_plain_bwd(x, dout, stats, gamma, dgamma, dbeta) -> torch.Tensor:
+    """BatchNorm backward without ReLU; stats = (4, C) tensor from bn_finalize."""
+    lib = N.require()
+    n, c, h, w = x.shape
+    sc = scratch(x.device)
+    dx = torch.empty_like(x)
+    N.check(lib.dpb_bn_plain_bwd(N.ptr(x), N.ptr(dout), N.ptr(stats[2]), N.ptr(stats[3]), N.ptr(gamma), N.ptr(sc.bn_part),
+                                 N.ptr(sc.bn_coef), N.ptr(dgamma), N.ptr(dbeta), N.ptr(dx), n * h * w, c, N.stream()),
+            "dpb_bn_plain_bwd")
+    N.count_launches(3)
+    return dx
+
+
 def linear_fwd(x, w, b) -> torch.Tensor:
     lib = N.require()
     bsz, k = x.shape

@@ -85,6 +85,28 @@ int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, 
                          float* coef, float* dgamma, float* dbeta, float* conv_dbias, float* dy, int n, int h, int w,
                          int c, int pool, dpb_stream_t stream);
 
+/* ---- The same layer types on their own (ref: model.py:16-25, any arrangement other than conv->bn->relu[->pool]) ---- */
+int dpb_relu_fwd(const float* x, float* y, long long n, dpb_stream_t stream);
+/* y: the forward OUTPUT (ReLU(inplace=True) keeps nothing else). */
+int dpb_relu_bwd(const float* y, const float* dout, float* dx, long long n, dpb_stream_t stream);
+int dpb_maxpool2x2_fwd(const float* x, float* out, int n, int h, int w, int c, dpb_stream_t stream);
+/* Routes each gradient to the first maximum of its window (aten's tie-break). */
+int dpb_maxpool2x2_bwd(const float* x, const float* dout, float* dx, int n, int h, int w, int c, dpb_stream_t stream);
+/* Per-block partial column sums / sums of squares of x[m][c] for dpb_bn_finalize: part_*: [dpb_column_stats_blocks()][c],
+ * *blocks_out rows are written (part_sq may be null). */
+int dpb_column_stats_blocks(void);
+int dpb_column_stats(const float* x, float* part_sum, float* part_sq, long long m, int c, int* blocks_out,
+                     dpb_stream_t stream);
+/* out[c] = sum over rows of x[m][c] (bias gradient of a lone conv); part: scratch [dpb_column_stats_blocks()][c]. */
+int dpb_column_sum(const float* x, float* part, float* out, long long m, int c, dpb_stream_t stream);
+/* y = x * scale + shift: BatchNorm without the ReLU. */
+int dpb_bn_apply(const float* x, const float* scale, const float* shift, float* y, long long m, int c,
+                 dpb_stream_t stream);
+/* BatchNorm backward without ReLU.  part: scratch [2][dpb_column_stats_blocks()][c]; coef: scratch [3][c]. */
+int dpb_bn_plain_bwd(const float* x, const float* dout, const float* save_mean, const float* save_invstd,
+                     const float* gamma, float* part, float* coef, float* dgamma, float* dbeta, float* dx, long long m,
+                     int c, dpb_stream_t stream);
+
 /* Allocation-free variant of dpb_bn_relu_pool_bwd.  (No counterpart in the reference: it exists for callers of this
  * library that cannot obtain device memory themselves -- a host program that talks only to this C ABI, or a plug-in
  * that is given input/output buffers and must not call cudaMalloc or any framework allocator.)
