@@ -38,7 +38,42 @@ splitk_reduce_kernel(const ConvGemmParams p, int NT, int m_tiles, int n_tiles, i
   if (MODE == kFprop && p.bias != nullptr) b = *reinterpret_cast<const float4*>(p.bias + col);
   float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
   const int r_end = blockIdx.y * R + R;
-  for (int r = blockIdx.y * R + rl; r < r_end; r += RL) {
+  int r = blockIdx.y * R + rl;
+  if (p.splits <= 4) {
+    // few splits: one row's loads do not cover the L2 latency, so take two rows per pass (up to 8 loads in flight)
+    for (; r + RL < r_end && m_tile * 128 + r + RL < p.M_total; r += 2 * RL) {
+      const float4* src0 = reinterpret_cast<const float4*>(wsb + (size_t)r * NT) + c4;
+      const float4* src1 = reinterpret_cast<const float4*>(wsb + (size_t)(r + RL) * NT) + c4;
+      float4 t0[4], t1[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (u < p.splits) {
+          t0[u] = __ldcg(src0 + (size_t)u * split_stride4);
+          t1[u] = __ldcg(src1 + (size_t)u * split_stride4);
+        }
+      }
+      float4 a0 = b, a1 = b;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (u < p.splits) {
+          f4_acc(a0, t0[u]);
+          f4_acc(a1, t1[u]);
+        }
+      }
+      const int g0 = m_tile * 128 + r, g1 = g0 + RL;
+      float* d0 = (MODE == kWgrad) ? p.out + (size_t)g0 * p.out_ld + (size_t)wtap * p.CinW + col
+                                   : p.out + (size_t)g0 * p.out_ld + col;
+      float* d1 = (MODE == kWgrad) ? p.out + (size_t)g1 * p.out_ld + (size_t)wtap * p.CinW + col
+                                   : p.out + (size_t)g1 * p.out_ld + col;
+      *reinterpret_cast<float4*>(d0) = a0;
+      *reinterpret_cast<float4*>(d1) = a1;
+      f4_acc(s0, a0);
+      s1.x += a0.x * a0.x; s1.y += a0.y * a0.y; s1.z += a0.z * a0.z; s1.w += a0.w * a0.w;
+      f4_acc(s0, a1);
+      s1.x += a1.x * a1.x; s1.y += a1.y * a1.y; s1.z += a1.z * a1.z; s1.w += a1.w * a1.w;
+    }
+  }
+  for (; r < r_end; r += RL) {
     const int grow = m_tile * 128 + r;
     if (grow >= p.M_total) break;
     const float4* src = reinterpret_cast<const float4*>(wsb + (size_t)r * NT) + c4;
