@@ -306,7 +306,7 @@ int dpb_linear_bwd(const float* dz, const float* x, const float* w, float* dx, f
     DPB_CUDA(launch_k(linear_bwd_input_kernel, dim3((int)((n + 255) / 256)), dim3(256), 0, S(stream), dz, w, dx, b, k, o));
   }
   if (dw != nullptr) {
-    DPB_CUDA(launch_k(linear_bwd_weight_kernel, dim3((k + 31) / 32), dim3(32, 8), 0, S(stream), dz, x, dw, db, b, k, o));
+    DPB_CUDA(launch_k(linear_bwd_weight_kernel, dim3((k + 31) / 32 + (db != nullptr ? 1 : 0)), dim3(32, 8), 0, S(stream), dz, x, dw, db, b, k, o));
   }
   return 0;
 }

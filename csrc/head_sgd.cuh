@@ -75,7 +75,7 @@ linear_bwd_input_kernel(const float* __restrict__ dz, const float* __restrict__ 
 }
 
 // dw[j][k] = sum_b dz[b][j] * x[b][k];  db[j] = sum_b dz[b][j].   grid = K/32 blocks of (32, 8); the batch is walked
-// by the 8 row lanes and combined in a fixed order.  Block 0 also produces db.
+// by the 8 row lanes and combined in a fixed order.  With db, the grid has one extra block that produces only db.
 __global__ void linear_bwd_weight_kernel(const float* __restrict__ dz, const float* __restrict__ x,
                                          float* __restrict__ dw, float* __restrict__ db, int B, int K, int O) {
   pdl_prologue();
@@ -86,8 +86,9 @@ __global__ void linear_bwd_weight_kernel(const float* __restrict__ dz, const flo
 #pragma unroll
   for (int j = 0; j < kMaxClasses; ++j) acc[j] = 0.f;
   if (k < K) {
+#pragma unroll 8
     for (int b = ry; b < B; b += 8) {
-      const float xv = x[(size_t)b * K + k];
+      const float xv = __ldg(x + (size_t)b * K + k);
 #pragma unroll
       for (int j = 0; j < kMaxClasses; ++j)
         if (j < O) acc[j] = fmaf(__ldg(dz + (size_t)b * O + j), xv, acc[j]);
@@ -104,7 +105,7 @@ __global__ void linear_bwd_weight_kernel(const float* __restrict__ dz, const flo
       dw[(size_t)j * K + k] = r;
     }
   }
-  if (blockIdx.x == 0 && db != nullptr) {
+  if (db != nullptr && blockIdx.x == gridDim.x - 1) {  // the extra block past the last k columns (see the launch)
     __syncthreads();
     const int t = ry * 32 + cx;  // 256 threads
     float a[kMaxClasses];
