@@ -79,3 +79,26 @@ def test_other_vgg_variants_build():
         assert sum(isinstance(x, torch.nn.Conv2d) for x in m.modules()) == n_conv
     out = dpb.VGG13().eval()(torch.randn(2, 3, 32, 32))
     assert out.shape == (2, 10)
+
+
+def test_modules_one_by_one_equal_the_fused_sequence_on_cpu():
+    """Walking `model.layers` module by module (what code written against the reference's nn.Sequential may do) gives
+    the same result as the FusedSequential forward; the functional entry points agree with torch.nn.functional."""
+    import torch.nn.functional as F
+    from distributed_pytorch_b200.ops import functional as Fn
+    torch.manual_seed(3)
+    model = dpb.VGG11()
+    x = torch.randn(4, 3, 32, 32)
+    fused = model.layers(x)
+    y = x
+    for m in model.layers:
+        y = m(y)
+    assert torch.allclose(fused, y, rtol=1e-5, atol=1e-6)
+    conv, bn = model.layers[0], model.layers[1]
+    assert torch.equal(Fn.conv3x3(x, conv.weight, conv.bias), F.conv2d(x, conv.weight, conv.bias, padding=1))
+    z = torch.randn(4, 64, 8, 8)
+    assert torch.equal(Fn.relu(z), F.relu(z)) and torch.equal(Fn.max_pool2x2(z), F.max_pool2d(z, 2, 2))
+    rm, rv, nbt = torch.zeros(64), torch.ones(64), torch.zeros((), dtype=torch.long)
+    out = Fn.batch_norm(z, bn.weight, bn.bias, rm, rv, nbt, True)
+    assert torch.allclose(out, F.batch_norm(z, None, None, bn.weight, bn.bias, True), rtol=1e-5, atol=1e-6)
+    assert int(nbt) == 1 and float(rm.abs().max()) > 0
