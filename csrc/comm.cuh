@@ -100,6 +100,8 @@ allreduce_twoshot_kernel(CommCtx c, int channel, PeerPtrs data, long long off4, 
                          int write_mean, SgdArgs sgd, PeerPtrs params, PeerPtrs mom) {
   const int rank = comm_rank<EMU>(c);
   const int nr = (NR > 0) ? NR : c.nranks;
+  const bool weak = (write_mean & 2) != 0;  // bit 1: weak payload accesses (dpb_set_tuning key 11), bit 0: write the mean
+  const bool wmean = (write_mean & 1) != 0;
   peer_barrier<EMU>(c, channel);
   const long long slice = (n4 + nr - 1) / nr;
   const long long lo = (long long)rank * slice;
@@ -117,8 +119,8 @@ allreduce_twoshot_kernel(CommCtx c, int channel, PeerPtrs data, long long off4, 
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const long long i = i0 + u * tstride;
-          v[r][u] = (i < hi) ? ld_peer_f4(reinterpret_cast<const float4*>(data.p[r]) + off4 + i)
-                             : make_float4(0.f, 0.f, 0.f, 0.f);
+          const float4* src = reinterpret_cast<const float4*>(data.p[r]) + off4 + i;
+          v[r][u] = (i < hi) ? (weak ? ld_peer_weak_f4(src) : ld_peer_f4(src)) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
       for (int r = 0; r < NR; ++r)
@@ -146,10 +148,16 @@ allreduce_twoshot_kernel(CommCtx c, int channel, PeerPtrs data, long long off4, 
         sgd1(pv.z, mv.z, acc[u].z, sgd);
         sgd1(pv.w, mv.w, acc[u].w, sgd);
         *ml = mv;
-        for (int r = 0; r < nr; ++r) st_peer_f4(reinterpret_cast<float4*>(params.p[r]) + off4 + i, pv);
+        for (int r = 0; r < nr; ++r) {
+          float4* dst = reinterpret_cast<float4*>(params.p[r]) + off4 + i;
+          if (weak) st_peer_weak_f4(dst, pv); else st_peer_f4(dst, pv);
+        }
       }
-      if (!sgd.enabled || write_mean) {
-        for (int r = 0; r < nr; ++r) st_peer_f4(reinterpret_cast<float4*>(data.p[r]) + off4 + i, acc[u]);
+      if (!sgd.enabled || wmean) {
+        for (int r = 0; r < nr; ++r) {
+          float4* dst = reinterpret_cast<float4*>(data.p[r]) + off4 + i;
+          if (weak) st_peer_weak_f4(dst, acc[u]); else st_peer_f4(dst, acc[u]);
+        }
       }
     }
   }

@@ -22,6 +22,7 @@ using namespace dpb;
 
 namespace {
 int g_tune_comm_blocks = 64;  // default grid cap of the collective kernels (dpb_set_tuning key 2)
+int g_tune_comm_weak = 0;     // two-shot all-reduce payload with weak (.cv load / plain store) accesses (key 11)
 inline cudaStream_t S(dpb_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 constexpr int kBnBwdBlocks = 296;
 constexpr int kFirstWgradBlocks = 444;  // rows of the first-layer wgrad partials buffer (= kFcTcMaxBlocks)
@@ -65,6 +66,7 @@ int dpb_set_tuning(int key, int value) {
   if (key == 8) { g_tune_pair_reduce = value ? 1 : 0; return 0; }
   if (key == 9 && value >= 0) { g_tune_tail_max_pixels = value; return 0; }
   if (key == 10 && value >= 0 && value <= 7) { g_tune_persistent = value; return 0; }
+  if (key == 11) { g_tune_comm_weak = value ? 1 : 0; return 0; }
   return set_error(-30, "dpb_set_tuning: bad key/value %d/%d", key, value);
 }
 
@@ -469,7 +471,7 @@ int dpb_allreduce_sgd(dpb_comm* c, int channel, void* const* grads, void* const*
 #define DPB_TWOSHOT(NRT, U)                                                                                      \
   return launch_comm(c, allreduce_twoshot_kernel<false, NRT, U>, allreduce_twoshot_kernel<true, NRT, U>,         \
                      comm_blocks_for(slice, 512, U, blocks), 512, st, c->ctx, channel, d, off4, n4, scale,        \
-                     write_mean, sg, pp, mm)
+                     (write_mean ? 1 : 0) | (g_tune_comm_weak ? 2 : 0), sg, pp, mm)
   switch (nr) {
     case 1: DPB_TWOSHOT(1, 4);
     case 2: DPB_TWOSHOT(2, 4);

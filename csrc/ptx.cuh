@@ -312,6 +312,16 @@ __device__ __forceinline__ float4 ld_peer_f4(const float4* p) {
                : "memory");
   return v;
 }
+// Weak (non-"strong") variants for bulk payload that is ordered by the surrounding system-scope barriers: loads that
+// bypass L1 (.cv: peer lines must never be served from a stale L1 line), plain stores.
+__device__ __forceinline__ float4 ld_peer_weak_f4(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.cv.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer_weak_f4(float4* p, const float4& v) {
+  asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 __device__ __forceinline__ void st_peer_f4(float4* p, const float4& v) {
   asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
                "f"(v.w)

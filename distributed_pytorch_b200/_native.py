@@ -146,7 +146,7 @@ def load(build_if_missing: bool = True):
                 build()
             lib = ctypes.CDLL(LIB_PATH)
             _bind(lib)
-            for key, env in ((0, "DPB_CONV_TARGET_CTAS"), (1, "DPB_CONV_NT"), (2, "DPB_COMM_BLOCKS"), (3, "DPB_CONV_MIN_K_ITERS"), (4, "DPB_PDL"), (5, "DPB_CONV_CLUSTER"), (6, "DPB_CONV_PAIR"), (7, "DPB_FIRST_TC"), (8, "DPB_PAIR_REDUCE"), (9, "DPB_TAIL_MAX_PIXELS"), (10, "DPB_CONV_PERSIST")):
+            for key, env in ((0, "DPB_CONV_TARGET_CTAS"), (1, "DPB_CONV_NT"), (2, "DPB_COMM_BLOCKS"), (3, "DPB_CONV_MIN_K_ITERS"), (4, "DPB_PDL"), (5, "DPB_CONV_CLUSTER"), (6, "DPB_CONV_PAIR"), (7, "DPB_FIRST_TC"), (8, "DPB_PAIR_REDUCE"), (9, "DPB_TAIL_MAX_PIXELS"), (10, "DPB_CONV_PERSIST"), (11, "DPB_COMM_WEAK")):
                 if os.environ.get(env):
                     lib.dpb_set_tuning(key, int(os.environ[env]))
             _lib = lib
