@@ -56,7 +56,12 @@ struct ConvGemmSmem {
   static constexpr int kStagingBytes = 128 * NT * 4;
   static_assert(kStagingBytes <= STAGES * kStageBytes, "staging must fit in the pipeline stages");
   static constexpr int kBarBytes = 256;
-  static constexpr int kTotal = 1024 /*align slack*/ + STAGES * kStageBytes + kBarBytes + 2 * NT * 4 * 4;
+  // per-warp column sums for the BatchNorm partials: also carved out of the drained stages (behind the staged tile)
+  // whenever they are large enough -- with 3 x 24 KB stages that lets THREE NT = 64 CTAs share an SM
+  static constexpr int kColredBytes = 2 * NT * 4 * 4;
+  static constexpr bool kColredAliased = kStagingBytes + kColredBytes <= STAGES * kStageBytes;
+  static constexpr int kColredOffset = kColredAliased ? kStagingBytes : STAGES * kStageBytes + kBarBytes;
+  static constexpr int kTotal = 1024 /*align slack*/ + STAGES * kStageBytes + kBarBytes + (kColredAliased ? 0 : kColredBytes);
 };
 
 // CL > 1: thread-block cluster of CL CTAs along blockIdx.x (neighbouring M tiles, same N tile / tap / split).  They
@@ -105,7 +110,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   uint64_t* empty_bar = bars + STAGES;     // [STAGES]
   uint64_t* acc_bar = bars + 2 * STAGES;   // [1]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
-  float* colred = reinterpret_cast<float*>(smem + STAGES * S::kStageBytes + S::kBarBytes);
+  float* colred = reinterpret_cast<float*>(smem + S::kColredOffset);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;

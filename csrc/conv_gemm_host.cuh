@@ -80,7 +80,9 @@ inline void pixel_box(int h, int w, int pixels, int* bw, int* bh, int* bn) {
 template <int MODE, int NT, int CL>
 int launch_conv_gemm_cl(const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
                         cudaStream_t stream) {
-  constexpr int STAGES = (NT == 128) ? 3 : 4;  // NT 64: 4 x 24 KB, NT 128: 3 x 32 KB (two CTAs per SM); NT 256: 4 x 48 KB
+  // NT 128: 3 x 32 KB (two CTAs per SM); NT 64: 3 x 24 KB (three CTAs per SM: the N = 64 MMA is issue-limited per CTA,
+  // see tools/mma_rate.cu, so more resident CTAs is what fills the tensor pipe); NT 256: 4 x 48 KB (one CTA per SM)
+  constexpr int STAGES = (NT == 256) ? 4 : 3;
   using S = ConvGemmSmem<NT, STAGES>;
   auto kern = conv_gemm_kernel<MODE, NT, STAGES, CL>;
   static bool attr_set = false;  // per instantiation
