@@ -61,6 +61,20 @@ inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_
   return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
+// Opt a kernel in to more than 48 KB of dynamic shared memory.  The attribute is per device, so remember (per call
+// site = per kernel instantiation) on which devices of this process it has been applied.
+#define DPB_SET_MAX_SMEM_ONCE(kern, bytes)                                                            \
+  do {                                                                                                \
+    static unsigned long long seen_ = 0;                                                              \
+    int dev_ = 0;                                                                                     \
+    DPB_CUDA(cudaGetDevice(&dev_));                                                                   \
+    const unsigned long long bit_ = 1ull << (dev_ & 63);                                              \
+    if (!(seen_ & bit_)) {                                                                            \
+      DPB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+      seen_ |= bit_;                                                                                  \
+    }                                                                                                 \
+  } while (0)
+
 // bring-up aid, set through dpb_debug_set_conv_dump()
 inline float* g_conv_debug_dump = nullptr;
 // kernels launched by the most recent conv_gemm_dispatch on this thread (1, or 2 with the split-K reduce)
@@ -85,11 +99,7 @@ int launch_conv_gemm_cl(const CUtensorMap& mA, const CUtensorMap& mB, const Conv
   constexpr int STAGES = (NT == 256) ? 4 : 3;
   using S = ConvGemmSmem<NT, STAGES>;
   auto kern = conv_gemm_kernel<MODE, NT, STAGES, CL>;
-  static bool attr_set = false;  // per instantiation
-  if (!attr_set) {
-    DPB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
-    attr_set = true;
-  }
+  DPB_SET_MAX_SMEM_ONCE(kern, S::kTotal);
   if (CL == 1) {
     DPB_CUDA(launch_k(kern, grid, dim3(192), S::kTotal, stream, mA, mB, p));
   } else {
@@ -126,11 +136,7 @@ int launch_conv_gemm_pair(const CUtensorMap& mA, const CUtensorMap& mB, const Co
   constexpr int STAGES = 4;  // per-CTA stage: 16 KB A + NT/2 x 128 B of B (NT 128: 96 KB, NT 256: 128 KB = the staged tile)
   using S = ConvGemmSmem<NT, STAGES, 2>;
   auto kern = conv_gemm_kernel<MODE, NT, STAGES, 1, 2>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DPB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
-    attr_set = true;
-  }
+  DPB_SET_MAX_SMEM_ONCE(kern, S::kTotal);
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid;
   cfg.blockDim = dim3(192);
@@ -173,11 +179,7 @@ int launch_conv_gemm_persistent(const CUtensorMap& mA, const CUtensorMap& mB, co
   constexpr int STAGES = (NT == 256) ? 4 : 6;  // NT 128: 6 x 32 KB, NT 64: 6 x 24 KB, NT 256: 4 x 48 KB
   using S = ConvPersistSmem<NT, STAGES>;
   auto kern = conv_gemm_persistent_kernel<MODE, NT, STAGES>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DPB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
-    attr_set = true;
-  }
+  DPB_SET_MAX_SMEM_ONCE(kern, S::kTotal);
   const int units = (int)(grid.x * grid.y * grid.z);
   const int ctas = units < device_sm_count() ? units : device_sm_count();
   DPB_CUDA(launch_k(kern, dim3(ctas), dim3(192), S::kTotal, stream, mA, mB, p, (int)grid.x, (int)grid.y, units));

@@ -103,11 +103,7 @@ int dpb_first_conv_fprop(const float* x, const float* weight, const float* bias,
                          float* part_sq, int n, int h, int w, dpb_stream_t stream) {
   const int blocks = dpb_first_conv_blocks(n, h, w);
   if (g_tune_first_tc && first_conv_tc_supported(h, w)) {
-    static bool attr_set = false;
-    if (!attr_set) {
-      DPB_CUDA(cudaFuncSetAttribute(first_conv_fprop_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FcTcSmem::kTotal));
-      attr_set = true;
-    }
+    DPB_SET_MAX_SMEM_ONCE(first_conv_fprop_tc_kernel, FcTcSmem::kTotal);
     DPB_CUDA(launch_k(first_conv_fprop_tc_kernel, dim3(blocks), dim3(kFcTcThreads), FcTcSmem::kTotal, S(stream), x, weight, bias, y, part_sum, part_sq, n, h, w));
     return 0;
   }
@@ -122,11 +118,7 @@ int dpb_first_conv_wgrad(const float* x, const float* dy, float* partials, float
                          dpb_stream_t stream) {
   const int nout = 64 * 27;
   if (g_tune_first_tc && first_conv_tc_supported(h, w)) {
-    static bool attr_set = false;
-    if (!attr_set) {
-      DPB_CUDA(cudaFuncSetAttribute(first_conv_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FcTcWgradSmem::kTotal));
-      attr_set = true;
-    }
+    DPB_SET_MAX_SMEM_ONCE(first_conv_wgrad_tc_kernel, FcTcWgradSmem::kTotal);
     const long long tiles = (long long)n * h * w / 128;
     const int blocks = (int)(tiles < kFcTcWgradMaxBlocks ? tiles : kFcTcWgradMaxBlocks);
     CUtensorMap map_dy;
