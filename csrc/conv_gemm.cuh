@@ -12,7 +12,7 @@
 //
 // Tile: 128 (M) x NT (N) per CTA, K consumed in chunks of 32 tf32 (one 128-byte swizzle row), 4 UMMA k-steps of 8.
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer, warps 2..5 =
-// epilogue (TMEM -> registers -> smem transpose -> coalesced 128-byte global rows).
+// epilogue (TMEM -> registers -> row-major XOR-swizzled tile in the drained stages -> whole 512-byte global rows).
 // Split-K: every split writes its fp32 partial tile to a workspace; splitk_reduce_kernel then sums the partials in split
 // order (deterministic) with the whole GPU, applies the bias and emits the per-channel sum / sum-of-squares partials that
 // the BatchNorm finalize kernel consumes.

@@ -6,11 +6,12 @@
 // [pixel rows][128 B], 32-byte unit u of row r stored at unit u ^ (r & 3).
 //   * A: the im2col row each thread builds for "its" pixel (as in the fprop kernel) IS one row of the A atom.
 //   * B: dY rows (64 channels = 256 B) are two atoms; TMA (SWIZZLE_128B_ATOM_32B, box 32 channels x 128 pixels)
-//     delivers them, three tiles ahead, so the 67 MB gradient stream never waits for the math.
+//     delivers them, up to two tiles ahead, so the 67 MB gradient stream does not wait for the math.
 // tcgen05.mma has no M = 32, so the instruction runs at M = 128 with the three upper A atoms pointing at whatever
 // follows in shared memory -- accumulator rows 32..127 are never read.  One TMEM accumulator lives across all tiles of
 // the CTA (the tensor core does the reduction over pixels); every CTA writes one [64 x 27] partial, summed in a fixed
-// order by column_reduce_kernel.  One CTA per SM: 2 A buffers + 3 dY stages = 128 KB of shared memory.
+// order by column_reduce_kernel.  Two CTAs per SM: 2 A buffers + 2 dY stages = 96 KB of shared memory each (a first
+// version with one CTA per SM and three stages was bound by instruction latency: one warp per scheduler).
 #pragma once
 #include <cuda.h>
 #include "first_conv_tc.cuh"
