@@ -10,6 +10,7 @@
 //           ->  bn_bwd_apply (dY = a*g + k1*y + k0).
 #pragma once
 #include "ptx.cuh"
+#include "bn_fold.cuh"
 
 namespace dpb {
 
@@ -228,6 +229,120 @@ bn_bwd_reduce_kernel(const float* __restrict__ y, const float* __restrict__ dout
     }
     reinterpret_cast<float4*>(part_g)[(size_t)blockIdx.x * C4 + threadIdx.x] = a;
     reinterpret_cast<float4*>(part_gx)[(size_t)blockIdx.x * C4 + threadIdx.x] = b;
+  }
+}
+
+// The same reduction with the finalize folded in (bn_fold.cuh).  grid = (C / 32 channel groups, slices); block = 256
+// threads = 8 float4 channel lanes x 32 pixel lanes, so a block touches only its group's 128 bytes of every pixel and the
+// block that delivers a group's last partial row can finish that group on its own: dgamma, dbeta, the preceding conv's
+// (exactly zero) bias gradient and the three coefficients of dY = a*g + k1*y + k0.  partials: part_g / part_gx are
+// [slices][C].  counters: one self-resetting ticket per channel group.
+template <bool POOL>
+__global__ void __launch_bounds__(256)
+bn_bwd_reduce_fold_kernel(const float* __restrict__ y, const float* __restrict__ dout, const float* __restrict__ scale,
+                          const float* __restrict__ shift, const float* __restrict__ mean,
+                          const float* __restrict__ invstd, const float* __restrict__ gamma,
+                          float* __restrict__ part_g, float* __restrict__ part_gx, long long out_pixels, int C, int H,
+                          int W, double count, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                          float* __restrict__ conv_dbias, float* __restrict__ coef, unsigned int* __restrict__ counters) {
+  pdl_prologue();
+  __shared__ __align__(16) unsigned char s_raw[2 * 256 * 16];  // [2][256] float4, later [2][8][32] doubles
+  __shared__ uint32_t s_flag;
+  float4* s_red = reinterpret_cast<float4*>(s_raw);
+  const int C4 = C >> 2;
+  const int cg = blockIdx.x;
+  const int cl = threadIdx.x & 7;   // float4 lane inside the 32-channel group
+  const int pl = threadIdx.x >> 3;  // pixel lane
+  const int c4 = cg * 8 + cl;
+  const float4 sc = __ldg(reinterpret_cast<const float4*>(scale) + c4);
+  const float4 sh = __ldg(reinterpret_cast<const float4*>(shift) + c4);
+  const float4 mu = __ldg(reinterpret_cast<const float4*>(mean) + c4);
+  const float4 is = __ldg(reinterpret_cast<const float4*>(invstd) + c4);
+  float4 sg = make_float4(0.f, 0.f, 0.f, 0.f), sgx = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float4* y4 = reinterpret_cast<const float4*>(y);
+  const float4* d4 = reinterpret_cast<const float4*>(dout);
+  for (long long op = (long long)blockIdx.y * 32 + pl; op < out_pixels; op += (long long)gridDim.y * 32) {
+    const float4 d = __ldg(d4 + op * C4 + c4);
+    if (POOL) {
+      const int Wo = W >> 1, Ho = H >> 1;
+      const int wo = (int)(op % Wo);
+      const long long t = op / Wo;
+      const int ho = (int)(t % Ho);
+      const long long n = t / Ho;
+      const long long p00 = (n * H + 2 * ho) * W + 2 * wo;
+      const float4 yy[4] = {__ldg(y4 + p00 * C4 + c4), __ldg(y4 + (p00 + 1) * C4 + c4),
+                            __ldg(y4 + (p00 + W) * C4 + c4), __ldg(y4 + (p00 + W + 1) * C4 + c4)};
+      float zx[4], zy[4], zz[4], zw[4], gx[4], gy[4], gz[4], gw[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float4 z = bn4(yy[i], sc, sh);
+        zx[i] = z.x; zy[i] = z.y; zz[i] = z.z; zw[i] = z.w;
+      }
+      pool_route(zx, d.x, gx); pool_route(zy, d.y, gy); pool_route(zz, d.z, gz); pool_route(zw, d.w, gw);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        sg.x += gx[i]; sg.y += gy[i]; sg.z += gz[i]; sg.w += gw[i];
+        sgx.x += gx[i] * (yy[i].x - mu.x) * is.x;
+        sgx.y += gy[i] * (yy[i].y - mu.y) * is.y;
+        sgx.z += gz[i] * (yy[i].z - mu.z) * is.z;
+        sgx.w += gw[i] * (yy[i].w - mu.w) * is.w;
+      }
+    } else {
+      const float4 yv = __ldg(y4 + op * C4 + c4);
+      const float4 z = bn4(yv, sc, sh);
+      const float4 g = make_float4(z.x > 0.f ? d.x : 0.f, z.y > 0.f ? d.y : 0.f, z.z > 0.f ? d.z : 0.f,
+                                   z.w > 0.f ? d.w : 0.f);
+      sg.x += g.x; sg.y += g.y; sg.z += g.z; sg.w += g.w;
+      sgx.x += g.x * (yv.x - mu.x) * is.x;
+      sgx.y += g.y * (yv.y - mu.y) * is.y;
+      sgx.z += g.z * (yv.z - mu.z) * is.z;
+      sgx.w += g.w * (yv.w - mu.w) * is.w;
+    }
+  }
+  s_red[threadIdx.x] = sg;
+  s_red[256 + threadIdx.x] = sgx;
+  __syncthreads();
+  if (threadIdx.x < 16) {  // 2 arrays x 8 channel lanes, pixel lanes added in lane order
+    const int which = threadIdx.x >> 3, l8 = threadIdx.x & 7;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int l = 0; l < 32; ++l) {
+      const float4 u = s_red[which * 256 + l * 8 + l8];
+      a.x += u.x; a.y += u.y; a.z += u.z; a.w += u.w;
+    }
+    float* dst = which == 0 ? part_g : part_gx;
+    reinterpret_cast<float4*>(dst)[(size_t)blockIdx.y * C4 + cg * 8 + l8] = a;
+  }
+  if (!arrive_last(counters + cg, gridDim.y, (int)threadIdx.x, 0, 256, &s_flag)) return;
+  // ---- this block saw the group's last partial row: finalize its 32 channels
+  double* s_d = reinterpret_cast<double*>(s_raw);  // [2][8][32]
+  const int T = (int)gridDim.y;
+  const int ch = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int c = cg * 32 + ch;
+  double a = 0.0, b = 0.0;
+  for (int t = rl; t < T; t += 8) {
+    a += (double)__ldcg(part_g + (size_t)t * C + c);
+    b += (double)__ldcg(part_gx + (size_t)t * C + c);
+  }
+  s_d[rl * 32 + ch] = a;
+  s_d[256 + rl * 32 + ch] = b;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    double sgd = 0.0, sgxd = 0.0;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      sgd += s_d[r * 32 + ch];
+      sgxd += s_d[256 + r * 32 + ch];
+    }
+    dgamma[c] = (float)sgxd;
+    dbeta[c] = (float)sgd;
+    if (conv_dbias != nullptr) conv_dbias[c] = 0.f;  // exactly zero, see bn_bwd_finalize_kernel
+    const double isd = (double)invstd[c];
+    const double ca = (double)gamma[c] * isd;
+    const double k1 = -ca * isd * sgxd / count;
+    const double k0 = -ca * sgd / count - k1 * (double)mean[c];
+    coef[c] = (float)ca;
+    coef[C + c] = (float)k1;
+    coef[2 * C + c] = (float)k0;
   }
 }
 

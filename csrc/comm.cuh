@@ -31,6 +31,7 @@ constexpr int kSigPadBytes = (kSigFlagsWords + kSigEpochWords) * 4;
 struct CommCtx {
   int rank;
   int nranks;
+  int withhold_rank;         // test hook (emulated worlds only): this virtual rank never signals; -1 = none
   uint32_t* sig[kMaxRanks];  // signal pad of every rank (peer mapped)
 };
 
@@ -49,6 +50,7 @@ template <bool EMU>
 __device__ __forceinline__ void peer_barrier(const CommCtx& c, int channel) {
   const int rank = comm_rank<EMU>(c);
   const int blk = blockIdx.x;
+  if (EMU && rank == c.withhold_rank) return;  // test hook: a rank that never shows up (its peers must time out)
   uint32_t* my_sig = c.sig[rank];
   uint32_t* epoch_p = my_sig + kSigFlagsWords + channel * kCommMaxBlocks + blk;
   __syncthreads();
@@ -59,10 +61,12 @@ __device__ __forceinline__ void peer_barrier(const CommCtx& c, int channel) {
     const int slot = (channel * kCommMaxBlocks + blk) * kMaxRanks;
     st_release_sys(c.sig[threadIdx.x] + slot + rank, e);
     const uint32_t* waitp = my_sig + slot + threadIdx.x;
-    const long long t0 = clock64();
+    const unsigned long long t0 = globaltimer_ns();
     uint32_t spins = 0;
     while ((int)(ld_acquire_sys(waitp) - e) < 0) {
-      if ((++spins & 0x3FF) == 0 && clock64() - t0 > 20000000000LL) dev_fail(2, channel, (int)threadIdx.x, (int)e);
+      // wall-clock budget; the record names who waited for whom (readable on the host even after the trap)
+      if ((++spins & 0xFF) == 0 && globaltimer_ns() - t0 > g_dpb_spin_timeout_ns)
+        dev_fail(2, channel, (int)threadIdx.x, (int)e, rank);
     }
   }
   __syncthreads();
@@ -162,6 +166,71 @@ allreduce_twoshot_kernel(CommCtx c, int channel, PeerPtrs data, long long off4, 
     }
   }
   peer_barrier<EMU>(c, channel);
+}
+
+// ------------------------------------------------------------------------------------------------ C3' NVLS two-shot
+// The same collective with the reduction done INSIDE the NVSwitch (NVLink SHARP): `mc` is the multicast view of the
+// gradient arena (csrc/vmm.cuh).  multimem.ld_reduce on an address of that view makes the switch fetch the 16 bytes
+// from every rank and return their sum; multimem.st writes 16 bytes to every rank.  Each GPU therefore receives 1/N of
+// the arena already reduced and sends it out once: about S bytes per direction per GPU instead of 2 (N-1)/N S with the
+// pull + push loops above, and an SM no longer pulls and pushes at the same time (the measured limit of that kernel,
+// profiles/microbench/nvlink_pull_push.txt).  Every rank stores the value the switch handed to the slice owner, so
+// replicas stay bit-identical.  With sgd.enabled the owner updates its slice of the LOCAL parameters / momentum and
+// multicasts the new parameters through `mc_params` (reference main_all_reduce.py:45-48 + optimizer.step()).
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float4* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float4* mc, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+
+template <int U>
+__global__ void __launch_bounds__(512)
+allreduce_nvls_kernel(CommCtx c, int channel, float* mc_grads, long long off4, long long n4, float scale, int write_mean,
+                      SgdArgs sgd, float* local_params, float* mc_params, float* local_mom) {
+  const int rank = c.rank;
+  const int nr = c.nranks;
+  peer_barrier<false>(c, channel);  // every rank's gradients are final
+  const long long slice = (n4 + nr - 1) / nr;
+  const long long lo = (long long)rank * slice;
+  long long hi = lo + slice;
+  if (hi > n4) hi = n4;
+  const long long tstride = (long long)gridDim.x * blockDim.x;
+  float4* mg = reinterpret_cast<float4*>(mc_grads) + off4;
+  for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < hi; i0 += tstride * U) {
+    float4 acc[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * tstride;
+      acc[u] = (i < hi) ? multimem_ld_reduce_f4(mg + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * tstride;
+      if (i >= hi) continue;
+      f4_scale(acc[u], scale);
+      if (sgd.enabled) {
+        float4* pl = reinterpret_cast<float4*>(local_params) + off4 + i;
+        float4* ml = reinterpret_cast<float4*>(local_mom) + off4 + i;
+        float4 pv = *pl, mv = *ml;
+        sgd1(pv.x, mv.x, acc[u].x, sgd);
+        sgd1(pv.y, mv.y, acc[u].y, sgd);
+        sgd1(pv.z, mv.z, acc[u].z, sgd);
+        sgd1(pv.w, mv.w, acc[u].w, sgd);
+        *ml = mv;
+        multimem_st_f4(reinterpret_cast<float4*>(mc_params) + off4 + i, pv);
+      }
+      if (!sgd.enabled || write_mean) multimem_st_f4(mg + i, acc[u]);
+    }
+  }
+  peer_barrier<false>(c, channel);  // the results have landed everywhere
 }
 
 // ------------------------------------------------------------------------------------------------ C2 one-shot

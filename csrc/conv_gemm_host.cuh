@@ -5,7 +5,6 @@
 #include <cuda_runtime.h>
 #include <mutex>
 #include "conv_gemm.cuh"
-#include "conv_gemm_persistent.cuh"
 #include "splitk_reduce.cuh"
 #include "errors.cuh"
 
@@ -75,8 +74,10 @@ inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_
     }                                                                                                 \
   } while (0)
 
+#ifdef DPB_EXPERIMENTS
 // bring-up aid, set through dpb_debug_set_conv_dump()
 inline float* g_conv_debug_dump = nullptr;
+#endif
 // kernels launched by the most recent conv_gemm_dispatch on this thread (1, or 2 with the split-K reduce)
 inline thread_local int g_conv_last_launches = 0;
 
@@ -91,190 +92,142 @@ inline void pixel_box(int h, int w, int pixels, int* bw, int* bh, int* bn) {
   *bn = rest / *bh;
 }
 
-template <int MODE, int NT, int CL>
-int launch_conv_gemm_cl(const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
+// cluster = true: the `p.splits` CTAs of a tile form a thread-block cluster along z and reduce over DSMEM (one launch);
+// otherwise splits > 1 goes through the workspace and splitk_reduce_kernel (two launches).
+template <int MODE, int NT>
+int launch_conv_gemm_nt(bool cluster, const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
                         cudaStream_t stream) {
   // NT 128: 3 x 32 KB (two CTAs per SM); NT 64: 3 x 24 KB (three CTAs per SM: the N = 64 MMA is issue-limited per CTA,
   // see tools/mma_rate.cu, so more resident CTAs is what fills the tensor pipe); NT 256: 4 x 48 KB (one CTA per SM)
   constexpr int STAGES = (NT == 256) ? 4 : 3;
   using S = ConvGemmSmem<NT, STAGES>;
-  auto kern = conv_gemm_kernel<MODE, NT, STAGES, CL>;
-  DPB_SET_MAX_SMEM_ONCE(kern, S::kTotal);
-  if (CL == 1) {
-    DPB_CUDA(launch_k(kern, grid, dim3(192), S::kTotal, stream, mA, mB, p));
-  } else {
+  if (cluster) {
+    auto kern = conv_gemm_kernel<MODE, NT, STAGES, true>;
+    DPB_SET_MAX_SMEM_ONCE(kern, S::kTotal);
+    if (p.splits > 8) {  // 16-CTA clusters are beyond the portable limit: opt in once per device
+      static unsigned long long seen = 0;
+      int dev = 0;
+      DPB_CUDA(cudaGetDevice(&dev));
+      if (!(seen & (1ull << (dev & 63)))) {
+        DPB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        seen |= 1ull << (dev & 63);
+      }
+    }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = grid;
     cfg.blockDim = dim3(192);
     cfg.dynamicSmemBytes = S::kTotal;
     cfg.stream = stream;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = CL;
+    at[0].val.clusterDim.x = 1;
     at[0].val.clusterDim.y = 1;
-    at[0].val.clusterDim.z = 1;
+    at[0].val.clusterDim.z = (unsigned)p.splits;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = g_tune_use_pdl ? 2 : 1;
     DPB_CUDA(cudaLaunchKernelEx(&cfg, kern, mA, mB, p));
+    g_conv_last_launches = 1;
+    return 0;
   }
-  const bool reduce_kernel = p.splits > 1 && !p.pair_reduce;
-  g_conv_last_launches = reduce_kernel ? 2 : 1;
-  if (reduce_kernel) {
-    const int m_tiles = grid.x, n_tiles = grid.y;
-    const int tiles = m_tiles * n_tiles * (MODE == kWgrad ? 9 : 1);
-    const int pieces = splitk_pieces(tiles, m_tiles, NT);
-    DPB_CUDA(launch_k(splitk_reduce_kernel<MODE>, dim3(tiles, pieces), dim3(256), 0, stream, p, NT, m_tiles, n_tiles, pieces));
-  }
-  return 0;
-}
-
-// CTA-pair variant (cta_group::2): cluster (2,1,1), each CTA stages half of B.  cl == kPairMode selects it.
-constexpr int kPairMode = -2;
-template <int MODE, int NT>
-int launch_conv_gemm_pair(const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
-                          cudaStream_t stream) {
-  constexpr int STAGES = 4;  // per-CTA stage: 16 KB A + NT/2 x 128 B of B (NT 128: 96 KB, NT 256: 128 KB = the staged tile)
-  using S = ConvGemmSmem<NT, STAGES, 2>;
-  auto kern = conv_gemm_kernel<MODE, NT, STAGES, 1, 2>;
+  auto kern = conv_gemm_kernel<MODE, NT, STAGES, false>;
   DPB_SET_MAX_SMEM_ONCE(kern, S::kTotal);
-  cudaLaunchConfig_t cfg{};
-  cfg.gridDim = grid;
-  cfg.blockDim = dim3(192);
-  cfg.dynamicSmemBytes = S::kTotal;
-  cfg.stream = stream;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = 2;
-  at[0].val.clusterDim.y = 1;
-  at[0].val.clusterDim.z = 1;
-  cfg.attrs = at;
-  cfg.numAttrs = 1;
-  DPB_CUDA(cudaLaunchKernelEx(&cfg, kern, mA, mB, p));
-  const bool reduce_kernel = p.splits > 1 && !p.pair_reduce;
-  g_conv_last_launches = reduce_kernel ? 2 : 1;
-  if (reduce_kernel) {
+  DPB_CUDA(launch_k(kern, grid, dim3(192), S::kTotal, stream, mA, mB, p));
+  g_conv_last_launches = 1;
+  if (p.splits > 1) {
     const int m_tiles = grid.x, n_tiles = grid.y;
     const int tiles = m_tiles * n_tiles * (MODE == kWgrad ? 9 : 1);
     const int pieces = splitk_pieces(tiles, m_tiles, NT);
     DPB_CUDA(launch_k(splitk_reduce_kernel<MODE>, dim3(tiles, pieces), dim3(256), 0, stream, p, NT, m_tiles, n_tiles, pieces));
+    g_conv_last_launches = 2;
   }
   return 0;
-}
-
-// Persistent variant (conv_gemm_persistent.cuh): one CTA per SM walks the work units the plain kernel would launch as
-// CTAs.  cl == kPersistMode selects it.
-constexpr int kPersistMode = -3;
-inline int device_sm_count() {
-  static int sms = 0;
-  if (sms == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
-      sms = 148;
-  }
-  return sms;
-}
-template <int MODE, int NT>
-int launch_conv_gemm_persistent(const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
-                                cudaStream_t stream) {
-  constexpr int STAGES = (NT == 256) ? 4 : 6;  // NT 128: 6 x 32 KB, NT 64: 6 x 24 KB, NT 256: 4 x 48 KB
-  using S = ConvPersistSmem<NT, STAGES>;
-  auto kern = conv_gemm_persistent_kernel<MODE, NT, STAGES>;
-  DPB_SET_MAX_SMEM_ONCE(kern, S::kTotal);
-  const int units = (int)(grid.x * grid.y * grid.z);
-  const int ctas = units < device_sm_count() ? units : device_sm_count();
-  DPB_CUDA(launch_k(kern, dim3(ctas), dim3(192), S::kTotal, stream, mA, mB, p, (int)grid.x, (int)grid.y, units));
-  const bool reduce_kernel = p.splits > 1;
-  g_conv_last_launches = reduce_kernel ? 2 : 1;
-  if (reduce_kernel) {
-    const int m_tiles = grid.x, n_tiles = grid.y;
-    const int tiles = m_tiles * n_tiles * (MODE == kWgrad ? 9 : 1);
-    const int pieces = splitk_pieces(tiles, m_tiles, NT);
-    DPB_CUDA(launch_k(splitk_reduce_kernel<MODE>, dim3(tiles, pieces), dim3(256), 0, stream, p, NT, m_tiles, n_tiles, pieces));
-  }
-  return 0;
-}
-
-template <int MODE, int NT>
-int launch_conv_gemm_nt(int cl, const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p, dim3 grid,
-                        cudaStream_t stream) {
-  if (cl == kPersistMode) return launch_conv_gemm_persistent<MODE, NT>(mA, mB, p, grid, stream);
-  if (cl == kPairMode) return launch_conv_gemm_pair<MODE, NT>(mA, mB, p, grid, stream);
-  if (cl == 2) return launch_conv_gemm_cl<MODE, NT, 2>(mA, mB, p, grid, stream);
-  if constexpr (NT >= 128) {
-    if (cl == 4) return launch_conv_gemm_cl<MODE, NT, 4>(mA, mB, p, grid, stream);
-  }
-  return launch_conv_gemm_cl<MODE, NT, 1>(mA, mB, p, grid, stream);
 }
 
 template <int MODE>
-int launch_conv_gemm_mode(int nt, int cl, const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p,
+int launch_conv_gemm_mode(int nt, bool cluster, const CUtensorMap& mA, const CUtensorMap& mB, const ConvGemmParams& p,
                           dim3 grid, cudaStream_t stream) {
   switch (nt) {
-    case 64: return launch_conv_gemm_nt<MODE, 64>(cl, mA, mB, p, grid, stream);
-    case 128: return launch_conv_gemm_nt<MODE, 128>(cl, mA, mB, p, grid, stream);
-    case 256: return launch_conv_gemm_nt<MODE, 256>(cl, mA, mB, p, grid, stream);
+    case 64: return launch_conv_gemm_nt<MODE, 64>(cluster, mA, mB, p, grid, stream);
+    case 128: return launch_conv_gemm_nt<MODE, 128>(cluster, mA, mB, p, grid, stream);
+    case 256: return launch_conv_gemm_nt<MODE, 256>(cluster, mA, mB, p, grid, stream);
   }
   return set_error(-12, "unsupported N tile %d", nt);
 }
 
-// Cluster size along M for B-tile multicast: the largest of {tuned value, 2, 1} that divides the M tiles and the B atoms.
-// g_tune_pair: use CTA pairs (cta_group::2) whenever the M tiles come in twos; returns kPairMode then.
-inline int g_tune_cluster = 1;
-inline int g_tune_pair = 0;
-inline int g_tune_persistent = 0;  // bit 0: fprop, bit 1: dgrad, bit 2: wgrad run the persistent kernel
-inline int pick_cluster(int m_tiles, int nt, int mode = 0) {
-  if ((g_tune_persistent >> mode) & 1) return kPersistMode;
-  if (g_tune_pair && m_tiles % 2 == 0 && (nt / 32) % 2 == 0) return kPairMode;
-  int cl = g_tune_cluster;
-  while (cl > 1 && (m_tiles % cl != 0 || (nt / 32) % cl != 0)) cl >>= 1;
-  return cl < 1 ? 1 : cl;
-}
-
-constexpr size_t kConvWorkspaceBytes = (size_t)48 << 20;  // split-K partial tiles
-constexpr int kConvCounterSlots = 8192;
+constexpr size_t kConvWorkspaceBytes = (size_t)48 << 20;  // split-K partial tiles (workspace path)
+constexpr int kConvCounterSlots = 8192;                  // ticket counters of the folded BatchNorm finalize
 
 // Number of CTAs we aim for: two waves of single-tile CTAs on 148 SMs.
 // Tunables (dpb_set_tuning): CTA count the split-K heuristic aims for, and the N tile used when the GEMM N extent allows it.
 inline int g_tune_target_ctas = 296;
 inline int g_tune_wide_nt = 128;
-inline int g_tune_min_k_iters = 8;  // k-iterations (of 32) a split must keep; fewer, fatter splits = less workspace traffic
-// Two-way splits finished inside the GEMM kernel (ConvGemmParams::pair_reduce).  Off: measured 1.010 vs 0.976 ms/step
-// at batch 256 although it removes 7 launches -- the second CTA's extra fence + 64 KB read + store sit on every
-// tile's critical path, while the separate reduce kernel spreads the same bytes over the whole GPU.
-inline int g_tune_pair_reduce = 0;
+inline int g_tune_min_k_iters = 8;  // k-iterations (of 32) a split must keep; fewer, fatter splits = less reduce traffic
+// Largest split factor that is reduced inside the GEMM kernel over distributed shared memory (thread-block cluster along
+// the split axis; 16 needs the non-portable cluster size).  1 sends every split-K GEMM through the workspace + reduce
+// kernel instead.
+inline int g_tune_cluster_max = 16;
+inline int g_tune_bn_fold = 1;  // BatchNorm finalize folded into the producer's last-arriving block
 
-inline int pick_splits(int tiles, int k_iters, int nt, int forced) {
-  int splits = 1;
+struct SplitPlan {
+  int splits;
+  bool cluster;
+};
+
+inline SplitPlan plan_splits(int tiles, int m_tiles, int k_iters, int nt, int forced) {
+  int want = 1;
   if (forced > 0) {
-    splits = forced;
+    want = forced;
   } else if (tiles < g_tune_target_ctas) {
-    splits = g_tune_target_ctas / tiles;
+    want = g_tune_target_ctas / tiles;
     int max_by_k = k_iters / g_tune_min_k_iters;  // keep a minimum amount of K per split
     if (max_by_k < 1) max_by_k = 1;
-    if (splits > max_by_k) splits = max_by_k;
+    if (want > max_by_k) want = max_by_k;
   }
-  if (splits > k_iters) splits = k_iters;
-  if (splits < 1) splits = 1;
+  if (want > k_iters) want = k_iters;
+  if (want < 1) want = 1;
+  SplitPlan sp{want, false};
+  if (want >= 2 && g_tune_cluster_max >= 2 && nt <= 128) {
+    int s = 2;
+    while (s * 2 <= want && s * 2 <= g_tune_cluster_max) s *= 2;
+    // heuristic choice: the power of two nearest to the wanted factor (6 -> 8, 5 -> 4), keeping >= 4 k-iterations a split
+    if (forced <= 0 && want * 2 >= s * 3 && s * 2 <= g_tune_cluster_max && s * 2 * 4 <= k_iters) s *= 2;
+    if (m_tiles > 64 && s > 4) s = 4;  // BatchNorm partial rows: callers size them for 4 rows per tile beyond 64 tiles
+    // forced: only an exact power of two goes to the cluster path (tests pick the path by the number they force);
+    // heuristic: the cluster path unless the GEMM wants far more splits than a cluster holds (early-layer wgrad)
+    const bool take = forced > 0 ? (s == want) : (want * 2 <= g_tune_cluster_max * 3);
+    if (take) {
+      sp.splits = s;
+      sp.cluster = true;
+      return sp;
+    }
+  }
   // workspace bound
-  while (splits > 1 && (size_t)tiles * splits * 128 * nt * 4 > kConvWorkspaceBytes) --splits;
-  return splits;
+  while (sp.splits > 1 && (size_t)tiles * sp.splits * 128 * nt * 4 > kConvWorkspaceBytes) --sp.splits;
+  return sp;
 }
 
 // mode: 0 fprop  (in = X[N,H,W,Cin], w = W[Cout,3,3,Cin], out = Y[N,H,W,Cout])
 //       1 dgrad  (in = dY[N,H,W,Cout], w = W, out = dX[N,H,W,Cin])
 //       2 wgrad  (in = dY[N,H,W,Cout], in2 = X[N,H,W,Cin], out = dW[Cout,3,3,Cin])
+// bn (fprop, optional): BatchNorm finalize arguments; *folded_out tells the caller whether the finalize ran inside
+// these launches (1) or still has to be launched over *out_stat_rows partial rows (0).
 inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, const float* in2, const float* w,
                               float* out, const float* bias, float* stat_sum, float* stat_sq, float* workspace,
-                              unsigned int* counters, int nt_override, int splits_override, int* out_m_tiles,
-                              cudaStream_t stream) {
+                              int nt_override, int splits_override, int* out_stat_rows, const BnFoldArgs* bn,
+                              int* folded_out, cudaStream_t stream) {
   if (g.cin % 32 || g.cout % 32) return set_error(-13, "conv_gemm needs Cin, Cout multiples of 32 (got %d, %d)", g.cin, g.cout);
   if (g.w > 32 || (g.w & (g.w - 1)) || (g.h & (g.h - 1))) return set_error(-13, "conv_gemm needs power-of-two H, W with W <= 32 (got %d x %d)", g.h, g.w);
   const long long pixels = (long long)g.n * g.h * g.w;
   ConvGemmParams p{};
   p.H = g.h; p.W = g.w; p.NImg = g.n; p.CinW = g.cin;
-  p.bias = bias; p.stat_sum = stat_sum; p.stat_sq = stat_sq; p.workspace = workspace; p.counters = counters;
+  p.bias = bias; p.stat_sum = stat_sum; p.stat_sq = stat_sq; p.workspace = workspace;
   p.out = out;
+#ifdef DPB_EXPERIMENTS
   p.debug_dump = g_conv_debug_dump;
+#endif
+  if (folded_out) *folded_out = 0;
   CUtensorMap mA, mB;
   dim3 grid;
   int nt;
@@ -284,30 +237,28 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
     const int cn = (mode == kFprop) ? g.cout : g.cin;   // GEMM N channels
     nt = nt_override > 0 ? nt_override : (cn % g_tune_wide_nt == 0 ? g_tune_wide_nt : (cn >= 128 ? 128 : 64));
     if (cn % nt) return set_error(-13, "N tile %d does not divide %d", nt, cn);
-    int bw, bh, bn;
-    pixel_box(g.h, g.w, 128, &bw, &bh, &bn);
-    p.box_w = bw; p.box_h = bh; p.box_n = bn;
+    int bw, bh, bn_;
+    pixel_box(g.h, g.w, 128, &bw, &bh, &bn_);
+    p.box_w = bw; p.box_h = bh; p.box_n = bn_;
     p.Ck = ck;
     p.M_total = (int)pixels; p.N_total = cn;
     p.k_iters = 9 * (ck / 32);
     p.out_ld = cn;
     const int m_tiles = (int)((pixels + 127) / 128);
     const int n_tiles = cn / nt;
-    p.splits = pick_splits(m_tiles * n_tiles, p.k_iters, nt, splits_override);
-    p.pair_reduce = (p.splits == 2 && g_tune_pair_reduce && m_tiles * n_tiles <= kConvCounterSlots) ? 1 : 0;
-    const int cl = pick_cluster(m_tiles, nt, mode);
-    if (cl == kPersistMode) p.pair_reduce = 0;  // the persistent kernel always leaves split-K to the reduce kernel
+    const SplitPlan sp = plan_splits(m_tiles * n_tiles, m_tiles, p.k_iters, nt, splits_override);
+    p.splits = sp.splits;
+    if (!sp.cluster && sp.splits > 1 && workspace == nullptr) return set_error(-13, "conv_gemm: split-K needs a workspace");
     {
       cuuint64_t dims[4] = {(cuuint64_t)ck, (cuuint64_t)g.w, (cuuint64_t)g.h, (cuuint64_t)g.n};
       cuuint64_t str[3] = {(cuuint64_t)ck * 4, (cuuint64_t)g.w * ck * 4, (cuuint64_t)g.h * g.w * ck * 4};
-      cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
+      cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn_};
       if ((rc = make_map_f32(&mA, in, 4, dims, str, box))) return rc;
     }
     if (mode == kFprop) {
       cuuint64_t dims[2] = {(cuuint64_t)9 * g.cin, (cuuint64_t)g.cout};
       cuuint64_t str[1] = {(cuuint64_t)9 * g.cin * 4};
-      // each CTA of a multicast cluster fetches nt/cl rows; each CTA of a pair stages nt/2 rows
-      cuuint32_t box[2] = {32, (cuuint32_t)(cl == kPairMode ? nt / 2 : (cl > 1 ? nt / cl : nt))};
+      cuuint32_t box[2] = {32, (cuuint32_t)nt};
       if ((rc = make_map_f32(&mB, w, 2, dims, str, box))) return rc;
     } else {
       cuuint64_t dims[2] = {(cuuint64_t)9 * g.cin, (cuuint64_t)g.cout};
@@ -316,25 +267,33 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
       if ((rc = make_map_f32(&mB, w, 2, dims, str, box, true))) return rc;
     }
     grid = dim3(m_tiles, n_tiles, p.splits);
-    if (out_m_tiles)  // BatchNorm partial rows written
-      *out_m_tiles = (p.splits > 1 && !p.pair_reduce) ? splitk_pieces(m_tiles * n_tiles, m_tiles, nt) * m_tiles : m_tiles;
-    if (mode == kFprop) return launch_conv_gemm_mode<kFprop>(nt, cl, mA, mB, p, grid, stream);
-    return launch_conv_gemm_mode<kDgrad>(nt, cl, mA, mB, p, grid, stream);
+    // BatchNorm partial rows written by these launches
+    p.stat_rows = sp.cluster ? m_tiles * sp.splits
+                             : (sp.splits > 1 ? splitk_pieces(m_tiles * n_tiles, m_tiles, nt) * m_tiles : m_tiles);
+    if (out_stat_rows) *out_stat_rows = p.stat_rows;
+    if (mode == kFprop && bn != nullptr && stat_sum != nullptr && bn->counters != nullptr && g_tune_bn_fold &&
+        p.stat_rows <= kBnFoldMaxRows && n_tiles <= kConvCounterSlots) {
+      p.bn = *bn;
+      if (folded_out) *folded_out = 1;
+    }
+    if (mode == kFprop) return launch_conv_gemm_mode<kFprop>(nt, sp.cluster, mA, mB, p, grid, stream);
+    return launch_conv_gemm_mode<kDgrad>(nt, sp.cluster, mA, mB, p, grid, stream);
   }
   // wgrad
   nt = nt_override > 0 ? nt_override : (g.cin % g_tune_wide_nt == 0 ? g_tune_wide_nt : (g.cin >= 128 ? 128 : 64));
   if (g.cin % nt) return set_error(-13, "N tile %d does not divide Cin %d", nt, g.cin);
-  int bw, bh, bn;
-  pixel_box(g.h, g.w, 32, &bw, &bh, &bn);
-  p.box_w = bw; p.box_h = bh; p.box_n = bn;
+  int bw, bh, bn_;
+  pixel_box(g.h, g.w, 32, &bw, &bh, &bn_);
+  p.box_w = bw; p.box_h = bh; p.box_n = bn_;
   p.Ck = 0;
   p.M_total = g.cout; p.N_total = g.cin;
   p.k_iters = (int)((pixels + 31) / 32);
   p.out_ld = (long long)9 * g.cin;
   const int m_tiles = (g.cout + 127) / 128;
   const int n_tiles = g.cin / nt;
-  p.splits = pick_splits(m_tiles * n_tiles * 9, p.k_iters, nt, splits_override);
-  p.pair_reduce = (p.splits == 2 && g_tune_pair_reduce && m_tiles * n_tiles * 9 <= kConvCounterSlots) ? 1 : 0;
+  const SplitPlan sp = plan_splits(m_tiles * n_tiles * 9, m_tiles, p.k_iters, nt, splits_override);
+  p.splits = sp.splits;
+  if (!sp.cluster && sp.splits > 1 && workspace == nullptr) return set_error(-13, "conv_gemm: split-K needs a workspace");
   {
     cuuint64_t dims[2] = {(cuuint64_t)g.cout, (cuuint64_t)pixels};
     cuuint64_t str[1] = {(cuuint64_t)g.cout * 4};
@@ -344,12 +303,12 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
   {
     cuuint64_t dims[4] = {(cuuint64_t)g.cin, (cuuint64_t)g.w, (cuuint64_t)g.h, (cuuint64_t)g.n};
     cuuint64_t str[3] = {(cuuint64_t)g.cin * 4, (cuuint64_t)g.w * g.cin * 4, (cuuint64_t)g.h * g.w * g.cin * 4};
-    cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
+    cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn_};
     if ((rc = make_map_f32(&mB, in2, 4, dims, str, box, true))) return rc;
   }
   grid = dim3(m_tiles, n_tiles, 9 * p.splits);
-  if (out_m_tiles) *out_m_tiles = m_tiles;
-  return launch_conv_gemm_mode<kWgrad>(nt, pick_cluster(m_tiles, nt, kWgrad), mA, mB, p, grid, stream);
+  if (out_stat_rows) *out_stat_rows = m_tiles;
+  return launch_conv_gemm_mode<kWgrad>(nt, sp.cluster, mA, mB, p, grid, stream);
 }
 
 }  // namespace dpb

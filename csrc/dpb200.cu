@@ -1,5 +1,6 @@
 // libdpb200.so: C ABI over the sm_100a kernels (see include/dpb200.h).  Single translation unit.
 #include <cstring>
+#include <mutex>
 #include <vector>
 #include <new>
 #include <cuda_runtime.h>
@@ -10,19 +11,24 @@
 #include "conv_gemm.cuh"
 #include "conv_gemm_host.cuh"
 #include "bn_relu_pool.cuh"
-#include "fused_tail.cuh"
 #include "standalone_ops.cuh"
 #include "first_conv.cuh"
 #include "first_conv_tc.cuh"
 #include "first_conv_tc_wgrad.cuh"
 #include "head_sgd.cuh"
 #include "comm.cuh"
+#include "augment.cuh"
+#include "vmm.cuh"
 
 using namespace dpb;
 
 namespace {
 int g_tune_comm_blocks = 64;  // default grid cap of the collective kernels (dpb_set_tuning key 2)
 int g_tune_comm_weak = 0;     // two-shot all-reduce payload with weak (.cv load / plain store) accesses (key 11)
+int g_tune_ddp_blocks = 24;   // grid of a per-bucket collective launched next to backward (key 13): few CTAs, so the
+                              // conv kernels it overlaps keep their SM slots
+int g_tune_nvls = 1;          // use the multimem (in-switch reduction) all-reduce when the buffers are multicast-bound (key 14)
+int g_tune_nvls_blocks = 32;  // its grid (key 15)
 inline cudaStream_t S(dpb_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 constexpr int kBnBwdBlocks = 296;
 constexpr int kFirstWgradBlocks = 444;  // rows of the first-layer wgrad partials buffer (= kFcTcMaxBlocks)
@@ -37,21 +43,65 @@ inline int grid_for(long long units, int threads, int cap) {
 
 extern "C" {
 
-int dpb_version(void) { return 100; }
+int dpb_version(void) { return 200; }
 const char* dpb_last_error(void) { return error_buffer(); }
 
-int dpb_last_device_error(int* out5) {
-  DevError e;
-  DPB_CUDA(cudaMemcpyFromSymbol(&e, g_dpb_dev_error, sizeof(e)));
-  out5[0] = e.code; out5[1] = e.where; out5[2] = e.block; out5[3] = e.aux0; out5[4] = e.aux1;
-  DevError z{};
-  DPB_CUDA(cudaMemcpyToSymbol(g_dpb_dev_error, &z, sizeof(z)));
+}  // extern "C"
+
+namespace {
+// One DevError record per device in mapped pinned host memory (see ptx.cuh): written by a kernel before it traps, read
+// here without any CUDA call, because after the trap the context only returns errors.
+constexpr int kMaxDevices = 64;
+DevError* g_host_err[kMaxDevices] = {nullptr};
+std::mutex g_init_mutex;
+unsigned long long g_peer_timeout_ns = 120000000000ull;
+
+int init_current_device() {
+  int dev = -1;
+  DPB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return set_error(-31, "device ordinal %d unsupported", dev);
+  std::lock_guard<std::mutex> lock(g_init_mutex);
+  if (g_host_err[dev] == nullptr) {
+    DevError* h = nullptr;
+    DPB_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&h), sizeof(DevError), cudaHostAllocMapped | cudaHostAllocPortable));
+    memset(h, 0, sizeof(DevError));
+    DevError* d = nullptr;
+    DPB_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&d), h, 0));
+    DPB_CUDA(cudaMemcpyToSymbol(g_dpb_dev_error_host, &d, sizeof(d)));
+    g_host_err[dev] = h;
+  }
+  DPB_CUDA(cudaMemcpyToSymbol(g_dpb_spin_timeout_ns, &g_peer_timeout_ns, sizeof(g_peer_timeout_ns)));
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+int dpb_init_device(void) { return init_current_device(); }
+
+int dpb_last_device_error(int device, int* out6) {
+  for (int i = 0; i < 6; ++i) out6[i] = 0;
+  for (int dev = 0; dev < kMaxDevices; ++dev) {
+    if (device >= 0 && dev != device) continue;
+    DevError* h = g_host_err[dev];
+    if (h == nullptr) continue;
+    volatile int* hv = reinterpret_cast<volatile int*>(h);
+    if (hv[0] == 0) continue;
+    for (int i = 0; i < 6; ++i) out6[i] = hv[i];
+    for (int i = 5; i >= 0; --i) hv[i] = 0;
+    return 0;
+  }
   return 0;
 }
 
 int dpb_debug_set_conv_dump(void* buf) {
+#ifdef DPB_EXPERIMENTS
   g_conv_debug_dump = reinterpret_cast<float*>(buf);
   return 0;
+#else
+  (void)buf;
+  return set_error(-30, "conv tracing is compiled out: rebuild libdpb200 with -DDPB_EXPERIMENTS");
+#endif
 }
 
 int dpb_set_tuning(int key, int value) {
@@ -60,13 +110,17 @@ int dpb_set_tuning(int key, int value) {
   if (key == 2 && value >= 1 && value <= kCommMaxBlocks) { g_tune_comm_blocks = value; return 0; }
   if (key == 3 && value >= 1) { g_tune_min_k_iters = value; return 0; }
   if (key == 4) { g_tune_use_pdl = value ? 1 : 0; return 0; }
-  if (key == 5 && (value == 1 || value == 2 || value == 4)) { g_tune_cluster = value; return 0; }
-  if (key == 6) { g_tune_pair = value ? 1 : 0; return 0; }
+  if (key == 5 && (value == 1 || value == 2 || value == 4 || value == 8 || value == 16)) { g_tune_cluster_max = value; return 0; }
   if (key == 7) { g_tune_first_tc = value ? 1 : 0; return 0; }
-  if (key == 8) { g_tune_pair_reduce = value ? 1 : 0; return 0; }
-  if (key == 9 && value >= 0) { g_tune_tail_max_pixels = value; return 0; }
-  if (key == 10 && value >= 0 && value <= 7) { g_tune_persistent = value; return 0; }
+  if (key == 8) { g_tune_bn_fold = value ? 1 : 0; return 0; }
   if (key == 11) { g_tune_comm_weak = value ? 1 : 0; return 0; }
+  if (key == 12 && value >= 1) {  // peer-signal wait budget in milliseconds; applied to the current device at once
+    g_peer_timeout_ns = (unsigned long long)value * 1000000ull;
+    return init_current_device();
+  }
+  if (key == 13 && value >= 1 && value <= kCommMaxBlocks) { g_tune_ddp_blocks = value; return 0; }
+  if (key == 14) { g_tune_nvls = value ? 1 : 0; return 0; }
+  if (key == 15 && value >= 1 && value <= kCommMaxBlocks) { g_tune_nvls_blocks = value; return 0; }
   return set_error(-30, "dpb_set_tuning: bad key/value %d/%d", key, value);
 }
 
@@ -78,11 +132,49 @@ size_t dpb_conv_counter_bytes(void) { return (size_t)kConvCounterSlots * sizeof(
 // ------------------------------------------------------------------------------------------------ convolution
 int dpb_conv3x3_gemm(int mode, int n, int h, int w, int cin, int cout, const float* in, const float* in2,
                      const float* weight, float* out, const float* bias, float* stat_sum, float* stat_sq,
-                     void* workspace, void* counters, int nt, int splits, int* m_tiles_out, dpb_stream_t stream) {
+                     void* workspace, int nt, int splits, int* stat_rows_out, dpb_stream_t stream) {
   if (mode < 0 || mode > 2) return set_error(-1, "dpb_conv3x3_gemm: bad mode %d", mode);
   ConvGeom g{n, h, w, cin, cout};
-  return conv_gemm_dispatch(mode, g, in, in2, weight, out, bias, stat_sum, stat_sq, (float*)workspace,
-                            (unsigned int*)counters, nt, splits, m_tiles_out, S(stream));
+  return conv_gemm_dispatch(mode, g, in, in2, weight, out, bias, stat_sum, stat_sq, (float*)workspace, nt, splits,
+                            stat_rows_out, nullptr, nullptr, S(stream));
+}
+
+static BnFoldArgs make_bn_args(const float* gamma, const float* beta, float* running_mean, float* running_var,
+                               long long* nbt, float momentum, float eps, double count, float* stats4, int c,
+                               void* counters) {
+  BnFoldArgs a{};
+  a.gamma = gamma; a.beta = beta; a.running_mean = running_mean; a.running_var = running_var;
+  a.num_batches_tracked = nbt; a.momentum = momentum; a.eps = eps; a.count = count;
+  a.scale = stats4; a.shift = stats4 + c; a.save_mean = stats4 + 2 * c; a.save_invstd = stats4 + 3 * c;
+  a.counters = reinterpret_cast<unsigned int*>(counters);
+  return a;
+}
+
+static int launch_bn_finalize(const float* ps, const float* pq, int rows, int c, const BnFoldArgs& a, cudaStream_t st) {
+  DPB_CUDA(launch_k(bn_finalize_kernel, dim3((c + kFinCh - 1) / kFinCh), dim3(kFinCh, kFinRows), 0, st, ps, pq, rows, c,
+                    a.count, a.gamma, a.beta, a.running_mean, a.running_var, a.num_batches_tracked, a.momentum, a.eps,
+                    a.scale, a.shift, a.save_mean, a.save_invstd));
+  return 0;
+}
+
+int dpb_conv3x3_fprop_bn(int n, int h, int w, int cin, int cout, const float* x, const float* weight, float* y,
+                         const float* bias, float* stat_sum, float* stat_sq, void* workspace, void* counters,
+                         const float* gamma, const float* beta, float* running_mean, float* running_var,
+                         long long* nbt, float momentum, float eps, float* stats4, int nt, int splits,
+                         dpb_stream_t stream) {
+  ConvGeom g{n, h, w, cin, cout};
+  const BnFoldArgs a = make_bn_args(gamma, beta, running_mean, running_var, nbt, momentum, eps, (double)n * h * w, stats4,
+                                    cout, counters);
+  int rows = 0, folded = 0;
+  int rc = conv_gemm_dispatch(kFprop, g, x, nullptr, weight, y, bias, stat_sum, stat_sq, (float*)workspace, nt, splits,
+                              &rows, &a, &folded, S(stream));
+  if (rc) return rc;
+  if (!folded) {
+    const int conv_launches = g_conv_last_launches;
+    if ((rc = launch_bn_finalize(stat_sum, stat_sq, rows, cout, a, S(stream)))) return rc;
+    g_conv_last_launches = conv_launches + 1;
+  }
+  return 0;
 }
 
 int dpb_first_conv_blocks(int n, int h, int w) {
@@ -99,16 +191,42 @@ static int first_conv_check(int w) {
   return 0;
 }
 
-int dpb_first_conv_fprop(const float* x, const float* weight, const float* bias, float* y, float* part_sum,
-                         float* part_sq, int n, int h, int w, dpb_stream_t stream) {
+static int first_conv_fprop_impl(const float* x, const float* weight, const float* bias, float* y, float* part_sum,
+                                 float* part_sq, int n, int h, int w, const BnFoldArgs& fold, cudaStream_t st) {
   const int blocks = dpb_first_conv_blocks(n, h, w);
   if (g_tune_first_tc && first_conv_tc_supported(h, w)) {
     DPB_SET_MAX_SMEM_ONCE(first_conv_fprop_tc_kernel, FcTcSmem::kTotal);
-    DPB_CUDA(launch_k(first_conv_fprop_tc_kernel, dim3(blocks), dim3(kFcTcThreads), FcTcSmem::kTotal, S(stream), x, weight, bias, y, part_sum, part_sq, n, h, w));
+    DPB_CUDA(launch_k(first_conv_fprop_tc_kernel, dim3(blocks), dim3(kFcTcThreads), FcTcSmem::kTotal, st, x, weight, bias, y, part_sum, part_sq, n, h, w, fold));
     return 0;
   }
   if (int rc = first_conv_check(w)) return rc;
-  DPB_CUDA(launch_k(first_conv_fprop_kernel, dim3(blocks), dim3(256), 0, S(stream), x, weight, bias, y, part_sum, part_sq, n, h, w));
+  DPB_CUDA(launch_k(first_conv_fprop_kernel, dim3(blocks), dim3(256), 0, st, x, weight, bias, y, part_sum, part_sq, n, h, w));
+  return 0;
+}
+
+int dpb_first_conv_fprop(const float* x, const float* weight, const float* bias, float* y, float* part_sum,
+                         float* part_sq, int n, int h, int w, dpb_stream_t stream) {
+  BnFoldArgs none{};
+  return first_conv_fprop_impl(x, weight, bias, y, part_sum, part_sq, n, h, w, none, S(stream));
+}
+
+int dpb_first_conv_fprop_bn(const float* x, const float* weight, const float* bias, float* y, float* part_sum,
+                            float* part_sq, int n, int h, int w, void* counters, const float* gamma, const float* beta,
+                            float* running_mean, float* running_var, long long* nbt, float momentum, float eps,
+                            float* stats4, dpb_stream_t stream) {
+  BnFoldArgs a = make_bn_args(gamma, beta, running_mean, running_var, nbt, momentum, eps, (double)n * h * w, stats4, 64,
+                              counters);
+  const int blocks = dpb_first_conv_blocks(n, h, w);
+  const bool fold = g_tune_bn_fold && counters != nullptr && g_tune_first_tc && first_conv_tc_supported(h, w) &&
+                    blocks <= kBnFoldMaxRows;
+  BnFoldArgs k = a;
+  if (!fold) k.counters = nullptr;
+  if (int rc = first_conv_fprop_impl(x, weight, bias, y, part_sum, part_sq, n, h, w, k, S(stream))) return rc;
+  g_conv_last_launches = 1;
+  if (!fold) {
+    if (int rc = launch_bn_finalize(part_sum, part_sq, blocks, 64, a, S(stream))) return rc;
+    g_conv_last_launches = 2;
+  }
   return 0;
 }
 
@@ -170,36 +288,46 @@ int dpb_bn_relu_pool_fwd(const float* y, const float* scale, const float* shift,
 
 int dpb_bn_bwd_blocks(void) { return kBnBwdBlocks; }
 
-int dpb_bn_bwd_launches(int n, int h, int w, int c, int pool) {
-  return tail_eligible((long long)n * h * w, c, h, w, pool != 0) ? 1 : 3;
+int dpb_bn_bwd_launches(int c, int with_counters) {
+  return (with_counters && g_tune_bn_fold && c % 32 == 0) ? 2 : 3;
 }
 
 int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, const float* shift,
                          const float* save_mean, const float* save_invstd, const float* gamma, float* part,
-                         float* coef, float* dgamma, float* dbeta, float* conv_dbias, float* dy, int n, int h, int w,
-                         int c, int pool, dpb_stream_t stream) {
+                         float* coef, void* counters, float* dgamma, float* dbeta, float* conv_dbias, float* dy, int n,
+                         int h, int w, int c, int pool, dpb_stream_t stream) {
   if (c % 4 || c > 1024) return set_error(-2, "bn_relu_pool_bwd: C must be a multiple of 4 and <= 1024 (got %d)", c);
-  if (tail_eligible((long long)n * h * w, c, h, w, pool != 0)) {  // small layer: one cluster kernel, no scratch
-    TailBwdParams tp{y, dout, scale, shift, save_mean, save_invstd, gamma, dy, dgamma, dbeta, conv_dbias, n * h * w, c, h, w};
-    if (pool) DPB_CUDA(launch_tail(tail_bwd_kernel<true>, tp, c, S(stream)));
-    else DPB_CUDA(launch_tail(tail_bwd_kernel<false>, tp, c, S(stream)));
-    return 0;
-  }
   const int c4 = c / 4;
   const long long opix = pool ? (long long)n * (h / 2) * (w / 2) : (long long)n * h * w;
-  const int pl = 256 / c4;
-  int blocks = (int)((opix + pl - 1) / pl);
-  if (blocks > kBnBwdBlocks) blocks = kBnBwdBlocks;
   float* part_g = part;
   float* part_gx = part + (size_t)kBnBwdBlocks * c;
-  const size_t smem = 2 * 256 * sizeof(float4);
-  if (pool) {
-    DPB_CUDA(launch_k(bn_bwd_reduce_kernel<true>, dim3(blocks), dim3(256), smem, S(stream), y, dout, scale, shift, save_mean, save_invstd, part_g, part_gx, opix, c4, h, w));
-  } else {
-    DPB_CUDA(launch_k(bn_bwd_reduce_kernel<false>, dim3(blocks), dim3(256), smem, S(stream), y, dout, scale, shift, save_mean, save_invstd, part_g, part_gx, opix, c4, h, w));
-  }
   const double count = (double)n * h * w;
-  DPB_CUDA(launch_k(bn_bwd_finalize_kernel, dim3((c + kFinCh - 1) / kFinCh), dim3(kFinCh, kFinRows), 0, S(stream), part_g, part_gx, blocks, c, count, gamma, save_mean, save_invstd, dgamma, dbeta, conv_dbias, coef));
+  if (counters != nullptr && g_tune_bn_fold && c % 32 == 0) {
+    // reduce + finalize in one launch: (C / 32) channel groups x slices, the last block of a group finishes it
+    const int groups = c / 32;
+    long long slices = (2 * kBnBwdBlocks) / groups;  // ~4 blocks per SM in total
+    const long long by_pixels = (opix + 31) / 32;
+    if (slices > by_pixels) slices = by_pixels;
+    if (slices > kBnBwdBlocks) slices = kBnBwdBlocks;
+    if (slices < 1) slices = 1;
+    unsigned int* cnt = reinterpret_cast<unsigned int*>(counters);
+    if (pool) {
+      DPB_CUDA(launch_k(bn_bwd_reduce_fold_kernel<true>, dim3(groups, (unsigned)slices), dim3(256), 0, S(stream), y, dout, scale, shift, save_mean, save_invstd, gamma, part_g, part_gx, opix, c, h, w, count, dgamma, dbeta, conv_dbias, coef, cnt));
+    } else {
+      DPB_CUDA(launch_k(bn_bwd_reduce_fold_kernel<false>, dim3(groups, (unsigned)slices), dim3(256), 0, S(stream), y, dout, scale, shift, save_mean, save_invstd, gamma, part_g, part_gx, opix, c, h, w, count, dgamma, dbeta, conv_dbias, coef, cnt));
+    }
+  } else {
+    const int pl = 256 / c4;
+    int blocks = (int)((opix + pl - 1) / pl);
+    if (blocks > kBnBwdBlocks) blocks = kBnBwdBlocks;
+    const size_t smem = 2 * 256 * sizeof(float4);
+    if (pool) {
+      DPB_CUDA(launch_k(bn_bwd_reduce_kernel<true>, dim3(blocks), dim3(256), smem, S(stream), y, dout, scale, shift, save_mean, save_invstd, part_g, part_gx, opix, c4, h, w));
+    } else {
+      DPB_CUDA(launch_k(bn_bwd_reduce_kernel<false>, dim3(blocks), dim3(256), smem, S(stream), y, dout, scale, shift, save_mean, save_invstd, part_g, part_gx, opix, c4, h, w));
+    }
+    DPB_CUDA(launch_k(bn_bwd_finalize_kernel, dim3((c + kFinCh - 1) / kFinCh), dim3(kFinCh, kFinRows), 0, S(stream), part_g, part_gx, blocks, c, count, gamma, save_mean, save_invstd, dgamma, dbeta, conv_dbias, coef));
+  }
   const long long units = opix * c4;
   const int ablocks = grid_for(units, 256, 148 * 16);
   if (pool) {
@@ -285,10 +413,45 @@ int dpb_bn_plain_bwd(const float* x, const float* dout, const float* save_mean, 
 }
 
 // ------------------------------------------------------------------------------------------------ head / loss
+static bool head_smem_ok(int k, int o) { return (k % 4 == 0) && (size_t)o * k * 4 <= 48 * 1024; }
+
 int dpb_linear_fwd(const float* x, const float* w, const float* bias, float* out, int b, int k, int o,
                    dpb_stream_t stream) {
   if (o > kMaxClasses) return set_error(-3, "linear: out_features %d > %d", o, kMaxClasses);
+  if (head_smem_ok(k, o)) {
+    DPB_CUDA(launch_k(head_fwd_kernel<false>, dim3((b + 7) / 8), dim3(256), (size_t)o * k * 4, S(stream), x, w, bias, (const long long*)nullptr, out, (float*)nullptr, (float2*)nullptr, (float*)nullptr, (float*)nullptr, (unsigned int*)nullptr, b, k, o));
+    return 0;
+  }
   DPB_CUDA(launch_k(linear_fwd_kernel, dim3((b * 32 + 127) / 128), dim3(128), 0, S(stream), x, w, bias, out, b, k, o));
+  return 0;
+}
+
+int dpb_head_supported(int k, int o) { return (o <= kMaxClasses && head_smem_ok(k, o)) ? 1 : 0; }
+
+int dpb_head_fwd(const float* x, const float* w, const float* bias, const long long* target, float* logits, float* dz,
+                 float* terms, float* loss, float* metrics, void* counter, int b, int k, int o, dpb_stream_t stream) {
+  if (!dpb_head_supported(k, o)) return set_error(-3, "head: unsupported shape K=%d O=%d", k, o);
+  DPB_CUDA(launch_k(head_fwd_kernel<true>, dim3((b + 7) / 8), dim3(256), (size_t)o * k * 4, S(stream), x, w, bias, target, logits, dz, reinterpret_cast<float2*>(terms), loss, metrics, reinterpret_cast<unsigned int*>(counter), b, k, o));
+  return 0;
+}
+
+int dpb_head_bwd(const float* dz, const float* x, const float* w, const float* grad_out, float* dx, float* dw,
+                 float* db, int b, int k, int o, dpb_stream_t stream) {
+  if (o > kMaxClasses) return set_error(-3, "head: out_features %d > %d", o, kMaxClasses);
+  const int nx = (int)(((long long)b * k + 255) / 256), nw = (k + 31) / 32;
+  DPB_CUDA(launch_k(head_bwd_kernel, dim3(nx + nw + 1), dim3(256), 0, S(stream), dz, x, w, grad_out, dx, dw, db, b, k, o, nx, nw));
+  return 0;
+}
+
+int dpb_augment_batch(const unsigned char* images, const long long* labels, const int* indices, int b, int h, int w,
+                      int train, unsigned int seed, unsigned int epoch, const int* draws, float mean0, float mean1,
+                      float mean2, float inv_std0, float inv_std1, float inv_std2, float* out_x, long long* out_y,
+                      dpb_stream_t stream) {
+  if (b <= 0) return 0;
+  if (w % 4) return set_error(-8, "augment: image width must be a multiple of 4 (got %d)", w);
+  AugmentNorm nrm{{mean0, mean1, mean2}, {inv_std0, inv_std1, inv_std2}};
+  augment_batch_kernel<<<b, 256, 0, S(stream)>>>(images, labels, indices, h, w, train, seed, epoch, draws, nrm, out_x, out_y);
+  DPB_CUDA(cudaGetLastError());
   return 0;
 }
 
@@ -365,6 +528,22 @@ int dpb_symm_close(void* peer_ptr) {
 }
 size_t dpb_signal_pad_bytes(void) { return kSigPadBytes; }
 
+// ---- the same through the virtual-memory-management API (csrc/vmm.cuh), which is what multicast needs
+int dpb_vmm_probe(int ndev, long long* out3) { return vmm_probe(ndev, out3); }
+int dpb_vmm_alloc(size_t bytes, size_t gran, void** ptr, unsigned long long* handle, int* fd) {
+  return vmm_alloc(bytes, gran, ptr, handle, fd);
+}
+int dpb_vmm_import(int fd, size_t bytes, size_t gran, int map, void** ptr, unsigned long long* handle) {
+  return vmm_import(fd, bytes, gran, map, ptr, handle);
+}
+int dpb_vmm_unmap(void* ptr, size_t bytes, unsigned long long handle) { return vmm_unmap(ptr, bytes, handle); }
+int dpb_mc_create(int ndev, size_t bytes, unsigned long long* handle, int* fd) { return mc_create(ndev, bytes, handle, fd); }
+int dpb_mc_add_device(unsigned long long mc) { return mc_add_device(mc); }
+int dpb_mc_bind_map(unsigned long long mc, unsigned long long mem, size_t bytes, size_t gran, void** mc_ptr) {
+  return mc_bind_map(mc, mem, bytes, gran, mc_ptr);
+}
+int dpb_mc_unbind(unsigned long long mc, size_t bytes) { return mc_unbind(mc, bytes); }
+
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------ communicator
@@ -436,6 +615,8 @@ int dpb_comm_create(int rank, int nranks, void* const* signal_pads, int emulate,
   if (!c) return set_error(-5, "comm: out of host memory");
   c->ctx.rank = rank;
   c->ctx.nranks = nranks;
+  c->ctx.withhold_rank = -1;
+  if (int rc = init_current_device()) { delete c; return rc; }
   for (int i = 0; i < kMaxRanks; ++i) c->ctx.sig[i] = i < nranks ? reinterpret_cast<uint32_t*>(signal_pads[i]) : nullptr;
   c->emulate = emulate;
   *out = c;
@@ -443,6 +624,11 @@ int dpb_comm_create(int rank, int nranks, void* const* signal_pads, int emulate,
 }
 int dpb_comm_destroy(dpb_comm* c) {
   delete c;
+  return 0;
+}
+int dpb_comm_debug_withhold(dpb_comm* c, int rank) {
+  if (!c->emulate) return set_error(-5, "comm: withholding a rank is a test hook of emulated worlds");
+  c->ctx.withhold_rank = rank;
   return 0;
 }
 
@@ -473,6 +659,34 @@ int dpb_allreduce_sgd(dpb_comm* c, int channel, void* const* grads, void* const*
   }
 #undef DPB_TWOSHOT
 }
+
+int dpb_allreduce_nvls(dpb_comm* c, int channel, void* mc_grads, void* local_params, void* mc_params, void* local_mom,
+                       long long offset, long long count, float scale, float lr, float mom, float wd, int nesterov,
+                       int write_mean, int blocks, dpb_stream_t stream) {
+  int rc = check_range("allreduce_nvls", offset, count);
+  if (rc) return rc;
+  if (count == 0) return 0;
+  if (c->emulate) return set_error(-4, "allreduce_nvls: multicast needs one GPU per rank (no single-GPU emulation)");
+  if (mc_grads == nullptr) return set_error(-4, "allreduce_nvls: the gradient buffer has no multicast mapping");
+  const int nr = c->ctx.nranks;
+  const long long n4 = count / 4, off4 = offset / 4;
+  SgdArgs sg{};
+  sg.enabled = local_params != nullptr;
+  sg.lr = lr; sg.momentum = mom; sg.wd = wd; sg.nesterov = nesterov;
+  if (sg.enabled && (mc_params == nullptr || local_mom == nullptr))
+    return set_error(-4, "allreduce_nvls: the fused optimizer needs multicast parameters and a momentum buffer");
+  constexpr int U = 4;
+  const long long slice = (n4 + nr - 1) / nr;
+  long long b = blocks > 0 ? blocks : (slice + 512LL * U - 1) / (512LL * U);
+  if (blocks <= 0 && b > g_tune_nvls_blocks) b = g_tune_nvls_blocks;
+  if (b > kCommMaxBlocks) b = kCommMaxBlocks;
+  if (b < 1) b = 1;
+  allreduce_nvls_kernel<U><<<(unsigned)b, 512, 0, S(stream)>>>(c->ctx, channel, (float*)mc_grads, off4, n4, scale, write_mean ? 1 : 0,
+                                                            sg, (float*)local_params, (float*)mc_params, (float*)local_mom);
+  DPB_CUDA(cudaGetLastError());
+  return 0;
+}
+int dpb_nvls_enabled(void) { return g_tune_nvls; }
 
 int dpb_allreduce(dpb_comm* c, int channel, void* const* bufs, long long offset, long long count, float scale,
                   int algo, int blocks, dpb_stream_t stream) {
@@ -547,6 +761,16 @@ struct dpb_reducer {
   std::vector<int> b_total, b_pending;
   std::vector<void*> bufs;
   float scale;
+  // optimizer fused into every bucket's collective (dpb_reducer_set_sgd): the slice owner updates parameters/momentum
+  bool sgd = false;
+  std::vector<void*> params, moms;
+  float lr = 0.f, mom = 0.f, wd = 0.f;
+  int nesterov = 0;
+  // multicast views (dpb_reducer_set_multicast): buckets are reduced inside the NVSwitch
+  void* mc_grads = nullptr;
+  void* mc_params = nullptr;
+  void* local_params = nullptr;
+  void* local_mom = nullptr;
   cudaStream_t side;
   cudaEvent_t ev_ready, ev_done;
   int launched;
@@ -585,7 +809,9 @@ int dpb_reducer_create(dpb_comm* c, int nparams, const long long* offsets, const
   r->bufs.assign(grad_bufs, grad_bufs + c->ctx.nranks);
   r->scale = scale;
   r->launched = 0;
-  if (cudaStreamCreateWithFlags(&r->side, cudaStreamNonBlocking) != cudaSuccess ||
+  int prio_lo = 0, prio_hi = 0;
+  cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);  // the collective's few CTAs go first when SM slots free up
+  if (cudaStreamCreateWithPriority(&r->side, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
       cudaEventCreateWithFlags(&r->ev_ready, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&r->ev_done, cudaEventDisableTiming) != cudaSuccess) {
     delete r;
@@ -604,6 +830,28 @@ int dpb_reducer_destroy(dpb_reducer* r) {
   return 0;
 }
 
+int dpb_reducer_set_sgd(dpb_reducer* r, void* const* param_bufs, void* const* mom_bufs, float lr, float momentum,
+                        float wd, int nesterov) {
+  const int nr = r->comm->ctx.nranks;
+  r->sgd = param_bufs != nullptr;
+  if (r->sgd) {
+    r->params.assign(param_bufs, param_bufs + nr);
+    r->moms.assign(mom_bufs, mom_bufs + nr);
+  }
+  r->lr = lr; r->mom = momentum; r->wd = wd; r->nesterov = nesterov;
+  return 0;
+}
+
+int dpb_reducer_set_multicast(dpb_reducer* r, void* mc_grads, void* mc_params, void* local_params, void* local_mom) {
+  r->mc_grads = mc_grads; r->mc_params = mc_params; r->local_params = local_params; r->local_mom = local_mom;
+  return 0;
+}
+
+int dpb_reducer_side_stream(dpb_reducer* r, dpb_stream_t* out) {
+  *out = reinterpret_cast<dpb_stream_t>(r->side);
+  return 0;
+}
+
 int dpb_reducer_prepare(dpb_reducer* r) {
   r->b_pending = r->b_total;
   r->launched = 0;
@@ -618,8 +866,18 @@ int dpb_reducer_mark_ready(dpb_reducer* r, int param, dpb_stream_t main_stream) 
   // bucket complete: side stream picks up after everything enqueued on the main stream so far
   DPB_CUDA(cudaEventRecord(r->ev_ready, S(main_stream)));
   DPB_CUDA(cudaStreamWaitEvent(r->side, r->ev_ready, 0));
-  int rc = dpb_allreduce(r->comm, /*channel=*/1, r->bufs.data(), r->b_lo[b], r->b_hi[b] - r->b_lo[b], r->scale,
-                         /*algo=*/0, /*blocks=*/0, r->side);
+  const long long lo = r->b_lo[b], cnt = r->b_hi[b] - r->b_lo[b];
+  int rc;
+  if (r->mc_grads != nullptr && g_tune_nvls && !r->comm->emulate && (!r->sgd || r->mc_params != nullptr)) {
+    rc = dpb_allreduce_nvls(r->comm, /*channel=*/1, r->mc_grads, r->sgd ? r->local_params : nullptr, r->mc_params,
+                            r->local_mom, lo, cnt, r->scale, r->lr, r->mom, r->wd, r->nesterov, /*write_mean=*/0,
+                            g_tune_ddp_blocks, r->side);
+  } else if (r->sgd) {
+    rc = dpb_allreduce_sgd(r->comm, /*channel=*/1, r->bufs.data(), r->params.data(), r->moms.data(), lo, cnt, r->scale,
+                           r->lr, r->mom, r->wd, r->nesterov, /*write_mean=*/0, g_tune_ddp_blocks, r->side);
+  } else {
+    rc = dpb_allreduce(r->comm, /*channel=*/1, r->bufs.data(), lo, cnt, r->scale, /*algo=*/0, g_tune_ddp_blocks, r->side);
+  }
   if (rc) return rc;
   r->launched++;
   return 0;
@@ -706,7 +964,8 @@ int dpb_bn_relu_pool_bwd_noalloc(const float* y, const float* dout, const float*
   // cleared even though the array still holds the previous call's contents.
   float* part = scratch;
   float* coef = scratch + (size_t)2 * kBnBwdBlocks * kNoAllocMaxChannels;
-  return dpb_bn_relu_pool_bwd(y, dout, scale, shift, save_mean, save_invstd, gamma, part, coef, dgamma, dbeta,
+  // (no ticket counters: this variant keeps the separate reduce / finalize / apply launches)
+  return dpb_bn_relu_pool_bwd(y, dout, scale, shift, save_mean, save_invstd, gamma, part, coef, nullptr, dgamma, dbeta,
                               conv_dbias, dy, n, h, w, c, pool, stream);
 }
 

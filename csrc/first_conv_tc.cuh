@@ -14,6 +14,7 @@
 // written once, in a fixed order: part_sum / part_sq are [gridDim.x][64].
 #pragma once
 #include "ptx.cuh"
+#include "bn_fold.cuh"
 
 namespace dpb {
 
@@ -72,10 +73,11 @@ __device__ __forceinline__ void fc_tc_fetch_patch(const float* __restrict__ x, i
 }
 
 // x: [N][3][H][W] fp32 (NCHW).  w: [64][3][3][3] (KRSC).  y: [N*H*W][64].  part_sum / part_sq: [gridDim.x][64] or null.
+// bn.counters != null: the CTA that writes the last partial row also performs the BatchNorm finalize (bn_fold.cuh).
 __global__ void __launch_bounds__(kFcTcThreads)
 first_conv_fprop_tc_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                            float* __restrict__ y, float* __restrict__ part_sum, float* __restrict__ part_sq, int N, int H,
-                           int W) {
+                           int W, const BnFoldArgs bn) {
   pdl_prologue();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_align_1024(smem_raw);
@@ -212,7 +214,15 @@ first_conv_fprop_tc_kernel(const float* __restrict__ x, const float* __restrict_
     }
     tc_fence_after();
   }
-  if (part_sum != nullptr) (tid < 64 ? part_sum : part_sq)[(size_t)blockIdx.x * 64 + (tid & 63)] = acc_stat;
+  if (part_sum != nullptr) {
+    (tid < 64 ? part_sum : part_sq)[(size_t)blockIdx.x * 64 + (tid & 63)] = acc_stat;
+    if (bn.counters != nullptr) {
+      volatile uint32_t* flag = slot + 1;
+      if (arrive_last(bn.counters, gridDim.x, tid, 0, kFcTcThreads, flag))
+        bn_finalize_cols(part_sum, part_sq, (int)gridDim.x, 64, 0, 64, bn, true, tid, 0, kFcTcThreads,
+                         reinterpret_cast<double*>(stg));
+    }
+  }
   __syncthreads();
   if (warp == 0) tmem_dealloc<64>(tmem);
 }

@@ -10,22 +10,48 @@
 
 namespace dpb {
 
-// Diagnostic record written by a kernel right before it gives up.  Host side reads it with
-// cudaMemcpyFromSymbol after a failed launch (see dpb_last_device_error in runtime.cu).
+// Diagnostic record written by a kernel right before it gives up.  The kernel writes it twice: into device memory
+// (g_dpb_dev_error) and -- because a trap leaves the CUDA context unusable, so device memory can no longer be read --
+// into a record in mapped pinned HOST memory that the runtime registers per device (dpb_init_device in dpb200.cu).  The
+// host reads that copy without any CUDA call (dpb_last_device_error).
 struct DevError {
   int code;        // 0 = none, 1 = mbarrier timeout, 2 = peer-signal timeout, 3 = bad argument
-  int where;       // call-site tag
+  int where;       // call-site tag (mbarrier: pipeline slot; peer signal: channel)
   int block;       // linear block id
-  int aux0, aux1;  // site specific (stage/parity, rank/slot, ...)
+  int aux0, aux1;  // site specific (stage/parity; rank waited for / epoch)
+  int rank;        // peer-signal timeout: the rank that was waiting
+  int reserved[2];
 };
 __device__ DevError g_dpb_dev_error;
+__device__ DevError* g_dpb_dev_error_host = nullptr;
+// Budget of a peer-signal wait in nanoseconds of %globaltimer (wall time, independent of the SM clock).  Default 120 s:
+// generous enough for a rank that is late because of a slow data shard or a debugger, short enough that a dead peer is
+// reported instead of hanging the job (dpb_set_tuning key 12 / DPB_PEER_TIMEOUT_S).
+__device__ unsigned long long g_dpb_spin_timeout_ns = 120000000000ull;
 
-__device__ __forceinline__ void dev_fail(int code, int where, int aux0, int aux1) {
-  g_dpb_dev_error.code = code;
-  g_dpb_dev_error.where = where;
-  g_dpb_dev_error.block = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
-  g_dpb_dev_error.aux0 = aux0;
-  g_dpb_dev_error.aux1 = aux1;
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__device__ __forceinline__ void dev_fail(int code, int where, int aux0, int aux1, int rank = -1) {
+  DevError e;
+  e.code = code;
+  e.where = where;
+  e.block = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  e.aux0 = aux0;
+  e.aux1 = aux1;
+  e.rank = rank;
+  e.reserved[0] = e.reserved[1] = 0;
+  g_dpb_dev_error = e;
+  DevError* h = g_dpb_dev_error_host;
+  if (h != nullptr) {
+    volatile int* hv = reinterpret_cast<volatile int*>(h);
+    hv[1] = e.where; hv[2] = e.block; hv[3] = e.aux0; hv[4] = e.aux1; hv[5] = e.rank;
+    __threadfence_system();
+    hv[0] = e.code;  // last: a non-zero code means the record is complete
+  }
   __threadfence_system();
   __trap();
 }
@@ -131,25 +157,6 @@ __device__ __forceinline__ void tma_load_5d(void* dst, const void* map, uint64_t
       : "memory");
 }
 
-// Multicast variants: the box lands at the same CTA-relative shared-memory offset in every CTA of `cta_mask`, and the
-// bytes are credited to the mbarrier at the same CTA-relative offset in each of them.
-__device__ __forceinline__ void tma_load_2d_mc(void* dst, const void* map, uint64_t* bar, int c0, int c1,
-                                               uint16_t cta_mask) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster"
-      " [%0], [%1, {%3, %4}], [%2], %5;"
-      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(cta_mask)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_4d_mc(void* dst, const void* map, uint64_t* bar, int c0, int c1, int c2,
-                                               int c3, uint16_t cta_mask) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster"
-      " [%0], [%1, {%3, %4, %5, %6}], [%2], %7;"
-      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "h"(cta_mask)
-      : "memory");
-}
-
 // ---------------------------------------------------------------- thread-block clusters
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -192,68 +199,27 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
 }
-// Same, arriving on the mbarrier at this CTA-relative offset in every CTA of `cta_mask` (cluster multicast).
-__device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t cta_mask) {
-  asm volatile(
-      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-      ::"r"(smem_u32(bar)), "h"(cta_mask)
-      : "memory");
-}
-// ---- CTA pairs (cta_group::2): two SMs of a cluster execute one 256-row MMA; the leader CTA (cluster rank 0) issues.
+// ---- distributed shared memory (thread-block clusters)
 // shared::cluster address of `p`'s offset inside CTA `cta` of the cluster
-__device__ __forceinline__ uint32_t mapa_u32(const void* p, uint32_t cta) {
+__device__ __forceinline__ uint32_t mapa_u32_addr(uint32_t cta_local_addr, uint32_t cta) {
   uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(cta));
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(cta_local_addr), "r"(cta));
   return r;
 }
-// fp32 load from another CTA's shared memory (address from mapa_u32)
+__device__ __forceinline__ uint32_t mapa_u32(const void* p, uint32_t cta) { return mapa_u32_addr(smem_u32(p), cta); }
+// loads from another CTA's shared memory (address from mapa_u32)
 __device__ __forceinline__ float ld_dsmem_f32(uint32_t cluster_addr) {
   float v;
   asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(cluster_addr) : "memory");
   return v;
 }
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-// TMA loads issued by either CTA of the pair into its OWN shared memory, bytes credited to the mbarrier at
-// `bar_cluster_addr` (the leader's).
-__device__ __forceinline__ void tma_load_2d_pair(void* dst, const void* map, uint32_t bar_cluster_addr, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(smem_u32(dst)), "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_4d_pair(void* dst, const void* map, uint32_t bar_cluster_addr, int c0, int c1,
-                                                 int c2, int c3) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-      ::"r"(smem_u32(dst)), "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-      : "memory");
-}
-template <int COLS>
-__device__ __forceinline__ void tmem_alloc_pair(uint32_t* smem_slot) {
-  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)), "n"(COLS)
+__device__ __forceinline__ float4 ld_dsmem_f4(uint32_t cluster_addr) {
+  float4 v;
+  asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(cluster_addr)
                : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-}
-template <int COLS>
-__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr) {
-  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(COLS) : "memory");
-}
-__device__ __forceinline__ void umma_tf32_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
-                                               uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n"
-      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit_pair_mc(uint64_t* bar, uint16_t cta_mask) {
-  asm volatile(
-      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-      ::"r"(smem_u32(bar)), "h"(cta_mask)
-      : "memory");
+  return v;
 }
 // 32 lanes x 32 consecutive fp32 columns: thread t of the warp receives lane (base_lane + t).
 __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, float (&v)[32]) {

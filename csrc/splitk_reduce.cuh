@@ -1,7 +1,11 @@
 // Second phase of split-K for the tcgen05 convolution.  The conv CTAs leave fp32 partial tiles in the workspace
 // ([tile][split][128][NT]); this kernel sums them in split order (deterministic), adds the bias, stores the result with
 // 16-byte accesses and leaves one BatchNorm partial row (sum, sum of squares per channel) per row piece of a tile:
-// stat row index = m_tile * pieces + piece.
+// stat row index = m_tile * pieces + piece.  The block that writes the last row of a channel group also performs the
+// BatchNorm finalize (bn_fold.cuh) when the caller asked for it.
+//
+// This is the fallback split-K path: GEMMs whose split factor fits a thread-block cluster (<= 16) are reduced over
+// distributed shared memory inside conv_gemm_kernel and never come here.
 //
 // grid = (tiles, pieces): one block owns R = 128 / pieces rows x NT columns of one tile; `pieces` is chosen by the host
 // so that even a layer with a handful of tiles (batch 32: one 128-row tile per 128 output channels, 36 splits) spreads
@@ -21,7 +25,9 @@ template <int MODE>
 __global__ void __launch_bounds__(256)
 splitk_reduce_kernel(const ConvGemmParams p, int NT, int m_tiles, int n_tiles, int pieces) {
   pdl_prologue();
-  __shared__ float4 red[2][256];
+  __shared__ __align__(16) unsigned char red_raw[256 * 64];  // [2][256] float4 column sums, later 2048 doubles for the finalize
+  __shared__ uint32_t last_flag;
+  float4 (*red)[256] = reinterpret_cast<float4 (*)[256]>(red_raw);
   const int tile_id = blockIdx.x;
   const int m_tile = tile_id % m_tiles;
   const int n_tile = (tile_id / m_tiles) % n_tiles;
@@ -103,6 +109,12 @@ splitk_reduce_kernel(const ConvGemmParams p, int NT, int m_tiles, int n_tiles, i
       for (int l = 0; l < RL; ++l) f4_acc(a, red[which][l * C4 + cc]);
       float* dst = which == 0 ? p.stat_sum : p.stat_sq;
       *reinterpret_cast<float4*>(dst + (size_t)(m_tile * pieces + blockIdx.y) * p.N_total + n_tile * NT + cc * 4) = a;
+    }
+    // BatchNorm finalize by the block that delivers the last partial row of this channel group (bn_fold.cuh)
+    if (p.bn.counters != nullptr) {
+      if (arrive_last(p.bn.counters + n_tile, (unsigned)(m_tiles * pieces), (int)threadIdx.x, 0, 256, &last_flag))
+        bn_finalize_cols(p.stat_sum, p.stat_sq, p.stat_rows, p.N_total, n_tile * NT, NT, p.bn, n_tile == 0,
+                         (int)threadIdx.x, 0, 256, reinterpret_cast<double*>(red_raw));
     }
   }
 }

@@ -25,6 +25,8 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC", "-shared", "-cudart", "static",
 ]
 
+ABI_VERSION = 200  # must equal dpb_version() of the loaded library (bumped whenever the C ABI changes)
+
 _lock = threading.Lock()
 _lib = None
 _load_error: str | None = None
@@ -38,28 +40,69 @@ def _sources() -> list[str]:
     return out
 
 
+HASH_PATH = LIB_PATH + ".srchash"
+
+
+def _source_hash() -> str:
+    import hashlib
+    h = hashlib.sha256()
+    for path in _sources():
+        h.update(os.path.basename(path).encode())
+        with open(path, "rb") as fh:
+            h.update(fh.read())
+    h.update(" ".join(NVCC_FLAGS).encode())
+    return h.hexdigest()
+
+
 def needs_build() -> bool:
-    if not os.path.exists(LIB_PATH):
+    """True if the library is missing or was built from other sources.  Compared by content hash (kept next to the
+    library), not by mtime: the tree may have been copied to another machine in any order."""
+    if not os.path.exists(LIB_PATH) or not os.path.exists(HASH_PATH):
         return True
-    t = os.path.getmtime(LIB_PATH)
-    return any(os.path.getmtime(s) > t for s in _sources())
+    try:
+        with open(HASH_PATH) as fh:
+            return fh.read().strip() != _source_hash()
+    except OSError:
+        return True
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile csrc/dpb200.cu for sm_100a into the in-tree shared library. Returns the library path."""
+def build(force: bool = False, verbose: bool = False, experiments: bool = False) -> str:
+    """Compile csrc/dpb200.cu for sm_100a into the in-tree shared library. Returns the library path.
+
+    Several ranks may get here at once on a fresh checkout (torchrun starts them together): the compile is serialised
+    with a file lock, goes to a temporary file and is moved into place atomically, so no process can dlopen a
+    half-written library; whoever gets the lock second finds the library up to date and returns.
+    ``experiments`` adds ``-DDPB_EXPERIMENTS`` (in-kernel tracing used by tools/conv_timing.py)."""
+    import fcntl
     if not force and not needs_build():
         return LIB_PATH
     os.makedirs(_LIBDIR, exist_ok=True)
-    nvcc = os.environ.get("NVCC", "nvcc")
-    cmd = [nvcc, *NVCC_FLAGS, "-o", LIB_PATH, os.path.join(_CSRC, "dpb200.cu")]
-    if verbose:
-        cmd.insert(1, "-Xptxas")
-        cmd.insert(2, "-v")
-    proc = subprocess.run(cmd, capture_output=True, text=True)
-    if proc.returncode != 0:
-        raise RuntimeError(f"nvcc failed ({' '.join(cmd)}):\n{proc.stdout}\n{proc.stderr}")
-    if verbose:
-        print(proc.stderr)
+    with open(os.path.join(_LIBDIR, ".build.lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not needs_build():
+                return LIB_PATH
+            nvcc = os.environ.get("NVCC", "nvcc")
+            tmp = f"{LIB_PATH}.tmp.{os.getpid()}"
+            cmd = [nvcc, *NVCC_FLAGS, "-o", tmp, os.path.join(_CSRC, "dpb200.cu")]
+            if experiments or os.environ.get("DPB_EXPERIMENTS") == "1":
+                cmd.insert(1, "-DDPB_EXPERIMENTS")
+            if verbose:
+                cmd.insert(1, "-Xptxas")
+                cmd.insert(2, "-v")
+            proc = subprocess.run(cmd, capture_output=True, text=True)
+            if proc.returncode != 0:
+                if os.path.exists(tmp):
+                    os.unlink(tmp)
+                raise RuntimeError(f"nvcc failed ({' '.join(cmd)}):\n{proc.stdout}\n{proc.stderr}")
+            os.replace(tmp, LIB_PATH)
+            with open(HASH_PATH + ".tmp", "w") as fh:
+                fh.write(_source_hash() + ("+experiments" if "-DDPB_EXPERIMENTS" in cmd else ""))
+            os.replace(HASH_PATH + ".tmp", HASH_PATH)
+            if verbose:
+                print(proc.stderr)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
     return LIB_PATH
 
 
@@ -71,11 +114,14 @@ _F = c_float
 _SIGNATURES = {
     "dpb_version": (c_int, []),
     "dpb_last_error": (c_char_p, []),
-    "dpb_last_device_error": (c_int, [POINTER(c_int)]),
+    "dpb_init_device": (c_int, []),
+    "dpb_last_device_error": (c_int, [_I, POINTER(c_int)]),
     "dpb_debug_set_conv_dump": (c_int, [_P]),
     "dpb_conv_workspace_bytes": (c_size_t, []),
     "dpb_conv_counter_bytes": (c_size_t, []),
-    "dpb_conv3x3_gemm": (c_int, [_I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, POINTER(c_int), _P]),
+    "dpb_conv3x3_gemm": (c_int, [_I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, POINTER(c_int), _P]),
+    "dpb_conv3x3_fprop_bn": (c_int, [_I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _F, _F, _P, _I, _I, _P]),
+    "dpb_first_conv_fprop_bn": (c_int, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _P, _P, _P, _P, _F, _F, _P, _P]),
     "dpb_conv_last_launches": (c_int, []),
     "dpb_set_tuning": (c_int, [_I, _I]),
     "dpb_first_conv_blocks": (c_int, [_I, _I, _I]),
@@ -86,8 +132,8 @@ _SIGNATURES = {
     "dpb_bn_eval_scale_shift": (c_int, [_I, _P, _P, _P, _P, _F, _P, _P, _P]),
     "dpb_bn_relu_pool_fwd": (c_int, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dpb_bn_bwd_blocks": (c_int, []),
-    "dpb_bn_bwd_launches": (c_int, [_I, _I, _I, _I, _I]),
-    "dpb_bn_relu_pool_bwd": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dpb_bn_bwd_launches": (c_int, [_I, _I]),
+    "dpb_bn_relu_pool_bwd": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dpb_relu_fwd": (c_int, [_P, _P, _LL, _P]),
     "dpb_relu_bwd": (c_int, [_P, _P, _P, _LL, _P]),
     "dpb_maxpool2x2_fwd": (c_int, [_P, _P, _I, _I, _I, _I, _P]),
@@ -103,6 +149,10 @@ _SIGNATURES = {
     "dpb_linear_bwd": (c_int, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "dpb_cross_entropy_fwd": (c_int, [_P, _P, _P, _P, _I, _I, _P]),
     "dpb_cross_entropy_bwd": (c_int, [_P, _P, _P, _P, _I, _I, _P]),
+    "dpb_head_supported": (c_int, [_I, _I]),
+    "dpb_head_fwd": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "dpb_head_bwd": (c_int, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "dpb_augment_batch": (c_int, [_P, _P, _P, _I, _I, _I, _I, ctypes.c_uint, ctypes.c_uint, _P, _F, _F, _F, _F, _F, _F, _P, _P, _P]),
     "dpb_sgd_step": (c_int, [_P, _P, _P, _LL, _F, _F, _F, _F, _I, _P]),
     "dpb_symm_alloc": (c_int, [c_size_t, POINTER(c_void_p)]),
     "dpb_symm_free": (c_int, [_P]),
@@ -110,6 +160,20 @@ _SIGNATURES = {
     "dpb_symm_import": (c_int, [ctypes.c_char_p, POINTER(c_void_p)]),
     "dpb_symm_close": (c_int, [_P]),
     "dpb_signal_pad_bytes": (c_size_t, []),
+    "dpb_vmm_probe": (c_int, [_I, POINTER(c_longlong)]),
+    "dpb_vmm_alloc": (c_int, [c_size_t, c_size_t, POINTER(c_void_p), POINTER(ctypes.c_ulonglong), POINTER(c_int)]),
+    "dpb_vmm_import": (c_int, [_I, c_size_t, c_size_t, _I, POINTER(c_void_p), POINTER(ctypes.c_ulonglong)]),
+    "dpb_vmm_unmap": (c_int, [_P, c_size_t, ctypes.c_ulonglong]),
+    "dpb_mc_create": (c_int, [_I, c_size_t, POINTER(ctypes.c_ulonglong), POINTER(c_int)]),
+    "dpb_mc_add_device": (c_int, [ctypes.c_ulonglong]),
+    "dpb_mc_bind_map": (c_int, [ctypes.c_ulonglong, ctypes.c_ulonglong, c_size_t, c_size_t, POINTER(c_void_p)]),
+    "dpb_mc_unbind": (c_int, [ctypes.c_ulonglong, c_size_t]),
+    "dpb_comm_debug_withhold": (c_int, [_P, _I]),
+    "dpb_allreduce_nvls": (c_int, [_P, _I, _P, _P, _P, _P, _LL, _LL, _F, _F, _F, _F, _I, _I, _I, _P]),
+    "dpb_nvls_enabled": (c_int, []),
+    "dpb_reducer_set_sgd": (c_int, [_P, POINTER(c_void_p), POINTER(c_void_p), _F, _F, _F, _I]),
+    "dpb_reducer_set_multicast": (c_int, [_P, _P, _P, _P, _P]),
+    "dpb_reducer_side_stream": (c_int, [_P, POINTER(c_void_p)]),
     "dpb_comm_create": (c_int, [_I, _I, POINTER(c_void_p), _I, POINTER(c_void_p)]),
     "dpb_comm_destroy": (c_int, [_P]),
     "dpb_allreduce": (c_int, [_P, _I, POINTER(c_void_p), _LL, _LL, _F, _I, _I, _P]),
@@ -128,6 +192,12 @@ _SIGNATURES = {
 }
 
 
+# dpb_set_tuning keys and the environment variables that set them at load time (include/dpb200.h)
+TUNING_ENV = ((0, "DPB_CONV_TARGET_CTAS"), (1, "DPB_CONV_NT"), (2, "DPB_COMM_BLOCKS"), (3, "DPB_CONV_MIN_K_ITERS"),
+              (4, "DPB_PDL"), (5, "DPB_CONV_CLUSTER_MAX"), (7, "DPB_FIRST_TC"), (8, "DPB_BN_FOLD"), (11, "DPB_COMM_WEAK"),
+              (13, "DPB_DDP_BLOCKS"), (14, "DPB_NVLS"), (15, "DPB_NVLS_BLOCKS"))
+
+
 def _bind(lib: ctypes.CDLL) -> None:
     for name, (res, args) in _SIGNATURES.items():
         fn = getattr(lib, name)
@@ -142,13 +212,24 @@ def load(build_if_missing: bool = True):
         if _lib is not None:
             return _lib
         try:
-            if not os.path.exists(LIB_PATH) and build_if_missing:
+            # a library older than its sources (a stale git-ignored .so from another checkout) is rebuilt, never loaded
+            if build_if_missing and needs_build():
                 build()
             lib = ctypes.CDLL(LIB_PATH)
+            lib.dpb_version.restype = c_int
+            if lib.dpb_version() != ABI_VERSION:
+                if not build_if_missing:
+                    raise RuntimeError(f"libdpb200.so has ABI version {lib.dpb_version()}, this package needs {ABI_VERSION}")
+                build(force=True)
+                lib = ctypes.CDLL(LIB_PATH)
+                lib.dpb_version.restype = c_int
+                if lib.dpb_version() != ABI_VERSION:
+                    raise RuntimeError(f"rebuilt libdpb200.so still reports ABI {lib.dpb_version()} (expected {ABI_VERSION})")
             _bind(lib)
-            for key, env in ((0, "DPB_CONV_TARGET_CTAS"), (1, "DPB_CONV_NT"), (2, "DPB_COMM_BLOCKS"), (3, "DPB_CONV_MIN_K_ITERS"), (4, "DPB_PDL"), (5, "DPB_CONV_CLUSTER"), (6, "DPB_CONV_PAIR"), (7, "DPB_FIRST_TC"), (8, "DPB_PAIR_REDUCE"), (9, "DPB_TAIL_MAX_PIXELS"), (10, "DPB_CONV_PERSIST"), (11, "DPB_COMM_WEAK")):
+            for key, env in TUNING_ENV:
                 if os.environ.get(env):
-                    lib.dpb_set_tuning(key, int(os.environ[env]))
+                    if lib.dpb_set_tuning(key, int(os.environ[env])) != 0 and key != 12:
+                        raise RuntimeError(f"{env}={os.environ[env]} rejected: {lib.dpb_last_error().decode()}")
             _lib = lib
             _load_error = None
         except Exception as exc:  # noqa: BLE001 - reported through load_error()/require()
@@ -176,11 +257,58 @@ class NativeError(RuntimeError):
     pass
 
 
+_initialised_devices: set[int] = set()
+
+
+def init_device(index: int | None = None) -> None:
+    """Register the device-error record and the peer time-out on a CUDA device (once per device and process)."""
+    import torch
+    idx = torch.cuda.current_device() if index is None else index
+    if idx in _initialised_devices:
+        return
+    lib = require()
+    with torch.cuda.device(idx):
+        if os.environ.get("DPB_PEER_TIMEOUT_MS"):
+            lib.dpb_set_tuning(12, int(os.environ["DPB_PEER_TIMEOUT_MS"]))
+        rc = lib.dpb_init_device()
+    if rc != 0:
+        raise NativeError(f"dpb_init_device failed (rc={rc}): {lib.dpb_last_error().decode()}")
+    _initialised_devices.add(idx)
+
+
+def device_error_message(device: int = -1) -> str | None:
+    """What a kernel of ours recorded before it gave up (None if nothing).  Works after the CUDA context has become
+    unusable, because the record lives in host memory."""
+    lib = load(build_if_missing=False)
+    if lib is None:
+        return None
+    out = (c_int * 6)()
+    lib.dpb_last_device_error(device, out)
+    code, where, block, aux0, aux1, rank = list(out)
+    if code == 0:
+        return None
+    if code == 2:
+        return (f"peer-signal timeout: rank {rank} waited for rank {aux0}, channel {where}, block {block}, "
+                f"epoch {aux1} (a peer never reached the collective: dead, hung or not launched)")
+    if code == 1:
+        return f"pipeline (mbarrier) timeout in a compute kernel: site {where}, block {block}, parity {aux0}"
+    return f"device error code {code}: where={where} block={block} aux=({aux0},{aux1})"
+
+
+def raise_if_device_error(exc: BaseException | None = None, device: int = -1) -> None:
+    """Turn a bare CUDA failure into the diagnostic our kernel left behind, if there is one."""
+    msg = device_error_message(device)
+    if msg is not None:
+        raise NativeError(msg) from exc
+
+
 def check(rc: int, what: str = "") -> None:
     if rc != 0:
         lib = require()
         msg = lib.dpb_last_error()
-        raise NativeError(f"{what or 'native call'} failed (rc={rc}): {msg.decode() if msg else ''}")
+        dev = device_error_message()
+        raise NativeError(f"{what or 'native call'} failed (rc={rc}): {msg.decode() if msg else ''}"
+                          + (f" [{dev}]" if dev else ""))
 
 
 # launch accounting (bench.py reports how many of our kernels ran inside the timed region)

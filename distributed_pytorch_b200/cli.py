@@ -51,8 +51,15 @@ def build_parser(mode: str) -> argparse.ArgumentParser:
     x.add_argument("--train-size", type=int, default=None)
     x.add_argument("--test-size", type=int, default=None)
     x.add_argument("--no-graph", action="store_true", help="run the step eagerly instead of as a CUDA graph")
-    x.add_argument("--fuse-optimizer", action="store_true",
-                   help="all_reduce mode: fuse the SGD update into the all-reduce kernel")
+    x.add_argument("--fuse-optimizer", dest="fuse_optimizer", action="store_true", default=True,
+                   help="all_reduce / ddp modes on CUDA: SGD update inside the collective kernel (default)")
+    x.add_argument("--no-fuse-optimizer", dest="fuse_optimizer", action="store_false",
+                   help="separate all-reduce and optimizer kernels")
+    x.add_argument("--overlap", action="store_true",
+                   help="all_reduce mode: reduce bucket by bucket on a side stream while backward is still running")
+    x.add_argument("--host-loader", action="store_true",
+                   help="augment on the host and copy batches (default on CUDA: dataset resident on the GPU, one "
+                        "augmentation kernel per batch)")
     x.add_argument("--save", default=None, help="write model state_dict (+ .optim) here at the end")
     x.add_argument("--load", default=None, help="load model state_dict (+ .optim) before training")
     x.add_argument("--quiet-nonzero", action="store_true", help="only rank 0 prints (the reference prints on all)")
@@ -99,8 +106,11 @@ def run(mode: str, argv: Optional[Sequence[str]] = None) -> dict:
     sampler = None
     if mode != "single":
         sampler = ShardedSampler(len(train_set), world, rank, shuffle=True, seed=0, drop_last=False)
-    train_loader = BatchLoader(train_set, batch, sampler=sampler, shuffle=(sampler is None), pin_memory=True)
-    test_loader = BatchLoader(test_set, batch, shuffle=False, pin_memory=True, max_batches=args.test_batches)
+    loader_dev = device if (device.type == "cuda" and not args.host_loader) else None
+    train_loader = BatchLoader(train_set, batch, sampler=sampler, shuffle=(sampler is None), pin_memory=True,
+                               device=loader_dev)
+    test_loader = BatchLoader(test_set, batch, shuffle=False, pin_memory=True, max_batches=args.test_batches,
+                              device=loader_dev)
 
     criterion = CrossEntropyLoss()
     model = VGG11().to(device)
@@ -108,10 +118,13 @@ def run(mode: str, argv: Optional[Sequence[str]] = None) -> dict:
     if mode in ("ddp", "part3"):
         model = DistributedDataParallel(model)
     optimizer = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=0.0001)
+    fuse = args.fuse_optimizer and device.type == "cuda"
+    if mode in ("ddp", "part3") and fuse:
+        model.fuse_optimizer(optimizer)
     if mode == "gather":
         sync = GatherScatterSync(model, world, rank)
     elif mode == "all_reduce":
-        sync = AllReduceSync(model, world, rank, fuse_optimizer=args.fuse_optimizer, optimizer=optimizer)
+        sync = AllReduceSync(model, world, rank, fuse_optimizer=fuse, optimizer=optimizer, overlap=args.overlap)
     else:
         sync = NoSync(model)
         if device.type == "cuda" and mode == "single":
@@ -130,6 +143,8 @@ def run(mode: str, argv: Optional[Sequence[str]] = None) -> dict:
     if args.save:
         if isinstance(sync, AllReduceSync):
             sync.gather_momentum()  # collective: every rank
+        if isinstance(model, DistributedDataParallel) and model.reducer is not None:
+            model.reducer.gather_momentum()
         if rank == 0:
             save_checkpoint(args.save, model, optimizer)
     if device.type == "cuda":

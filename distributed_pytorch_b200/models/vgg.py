@@ -124,6 +124,14 @@ class VGG(nn.Module):
         y = y.reshape(y.size(0), -1)
         return self.fc1(y)
 
+    def forward_loss(self, x, target):
+        """``CrossEntropyLoss()(self(x), target)`` with the classifier and the loss fused into one kernel each way
+        (reference main.py:33-35: ``output = model(data); loss = criterion(output, target)``).  Returns the loss."""
+        y = self.layers(x)
+        y = y.reshape(y.size(0), -1)
+        loss, _ = Fn.linear_cross_entropy(y, self.fc1.weight, self.fc1.bias, target)
+        return loss
+
 
 def VGG11() -> VGG:
     return VGG("VGG11")

@@ -23,7 +23,7 @@ import torch.nn.functional as F
 from . import kernels as K
 
 __all__ = ["conv_bn_relu_pool", "conv3x3", "batch_norm", "relu", "max_pool2x2", "linear", "cross_entropy",
-           "grad_destination"]
+           "linear_cross_entropy", "grad_destination"]
 
 
 def grad_destination(param: torch.Tensor) -> torch.Tensor:
@@ -63,12 +63,13 @@ class _ConvBnReluPool(torch.autograd.Function):
             xin = _as_nhwc(x.detach())
         y = K.nhwc_empty(n, cout, h, w, x.device)
         if training:
+            # conv + batch statistics; the finalize (scale/shift, running stats) is folded into the producing kernel
             if first:
-                ps, pq, parts = K.first_conv_fprop(xin, wk, conv_b, y, True)
+                stats = K.first_conv_fprop_bn(xin, wk, conv_b, y, bn_w, bn_b, running_mean, running_var, nbt, momentum,
+                                              eps)
             else:
-                ps, pq, parts = K.conv3x3_gemm(0, n, h, w, cin, cout, xin, None, wk, y, conv_b, want_stats=True)
-            stats = K.bn_finalize(ps, pq, parts, cout, float(n * h * w), bn_w, bn_b, running_mean, running_var, nbt,
-                                  momentum, eps)
+                stats = K.conv3x3_fprop_bn(n, h, w, cin, cout, xin, wk, y, conv_b, bn_w, bn_b, running_mean,
+                                           running_var, nbt, momentum, eps)
         else:
             if first:
                 K.first_conv_fprop(xin, wk, conv_b, y, False)
@@ -310,6 +311,43 @@ def linear(x, w, b):
     if x.is_cuda:
         return _Linear.apply(x, w, b)
     return F.linear(x, w, b)
+
+
+class _HeadLoss(torch.autograd.Function):
+    """Linear -> mean cross-entropy as two launches (forward, backward) instead of five: the forward kernel also leaves
+    dz = dLoss/dlogits for a unit upstream gradient, the backward kernel scales by autograd's grad_output and produces
+    dx, dW and db together."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, target):
+        xc = x.detach().contiguous()
+        wc = w.detach().contiguous()
+        tg = target.contiguous()
+        loss, logits, dz = K.head_fwd(xc, wc, b, tg)
+        ctx.params = (w, b)
+        ctx.save_for_backward(xc, wc, dz)
+        ctx.mark_non_differentiable(logits)
+        return loss, logits
+
+    @staticmethod
+    def backward(ctx, gout, _glogits):
+        xc, wc, dz = ctx.saved_tensors
+        w, b = ctx.params
+        dx = torch.empty_like(xc) if ctx.needs_input_grad[0] else None
+        dw = grad_destination(w)
+        db = grad_destination(b) if b is not None else None
+        K.head_bwd(dz, xc, wc, gout.contiguous(), dx, dw, db)
+        return dx, dw, db, None
+
+
+def linear_cross_entropy(x, w, b, target):
+    """``cross_entropy(linear(x, w, b), target)`` fused (reference model.py:45 + main.py:34); returns (loss, logits)."""
+    if x.is_cuda and b is not None and K.head_supported(x.shape[1], w.shape[0]):
+        if target.dtype != torch.int64:
+            target = target.long()
+        return _HeadLoss.apply(x, w, b, target)
+    logits = linear(x, w, b)
+    return cross_entropy(logits, target), logits
 
 
 class _CrossEntropy(torch.autograd.Function):

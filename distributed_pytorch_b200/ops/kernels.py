@@ -15,8 +15,9 @@ import torch
 from .. import _native as N
 
 __all__ = [
-    "Scratch", "scratch", "conv3x3_gemm", "first_conv_fprop", "first_conv_wgrad", "bn_finalize", "bn_eval_scale_shift",
-    "bn_relu_pool_fwd", "bn_relu_pool_bwd", "linear_fwd", "linear_bwd", "cross_entropy_fwd", "cross_entropy_bwd",
+    "Scratch", "scratch", "conv3x3_gemm", "conv3x3_fprop_bn", "first_conv_fprop", "first_conv_fprop_bn",
+    "first_conv_wgrad", "bn_finalize", "bn_eval_scale_shift", "bn_relu_pool_fwd", "bn_relu_pool_bwd", "linear_fwd",
+    "linear_bwd", "cross_entropy_fwd", "cross_entropy_bwd", "head_supported", "head_fwd", "head_bwd", "augment_batch",
     "sgd_step", "is_nhwc", "nhwc_empty",
 ]
 
@@ -34,18 +35,21 @@ def nhwc_empty(n: int, c: int, h: int, w: int, device) -> torch.Tensor:
 
 
 class Scratch:
-    """Per-device scratch the kernels share (stream-ordered reuse): split-K partial tiles and arrival counters for
-    the tensor-core conv, BatchNorm-backward partial sums and coefficients, first-layer wgrad partials."""
+    """Per-device scratch the kernels share (stream-ordered reuse): split-K partial tiles of the workspace path,
+    self-resetting ticket counters of the folded finalize steps, BatchNorm-backward partial sums and coefficients,
+    first-layer wgrad partials."""
 
     def __init__(self, device: torch.device):
         lib = N.require()
+        N.init_device(device.index)
         self.device = device
         self.conv_ws = torch.empty(lib.dpb_conv_workspace_bytes() // 4, device=device, dtype=torch.float32)
         self.conv_counters = torch.zeros(lib.dpb_conv_counter_bytes() // 4, device=device, dtype=torch.int32)
+        self.bn_counters = torch.zeros(64, device=device, dtype=torch.int32)
+        self.head_counter = torch.zeros(4, device=device, dtype=torch.int32)
         # second split-K workspace: weight-gradient GEMMs running on the side stream (WgradLane) must not share partial
         # tiles with the data-gradient GEMM that runs next to them
         self.conv_ws_side = None
-        self.conv_counters_side = None
         self.bn_blocks = lib.dpb_bn_bwd_blocks()
         self.bn_part = torch.empty(2 * self.bn_blocks * 1024, device=device, dtype=torch.float32)
         self.bn_coef = torch.empty(3 * 1024, device=device, dtype=torch.float32)
@@ -90,7 +94,6 @@ class WgradLane:
         sc = scratch(device)
         if sc.conv_ws_side is None:
             sc.conv_ws_side = torch.empty_like(sc.conv_ws)
-            sc.conv_counters_side = torch.zeros_like(sc.conv_counters)
 
     def fork(self) -> None:
         self._fork_ev.record(torch.cuda.current_stream(self.device))
@@ -152,22 +155,43 @@ def conv3x3_gemm(mode: int, n: int, h: int, w: int, cin: int, cout: int, inp: to
     with ``want_stats`` else None.  ``side`` selects the second split-K workspace (see :class:`WgradLane`)."""
     lib = N.require()
     sc = scratch(out.device)
-    conv_ws, conv_counters = (sc.conv_ws_side, sc.conv_counters_side) if side else (sc.conv_ws, sc.conv_counters)
+    conv_ws = sc.conv_ws_side if side else sc.conv_ws
     stat_sum = stat_sq = None
     m_tiles = ctypes.c_int(0)
     if want_stats:
-        tiles = (n * h * w + 127) // 128
-        tiles *= 32 if tiles <= 64 else 4  # split-K leaves up to 32 (<= 64 tiles) / 4 partial rows per tile, else 1
-        stat_sum = torch.empty((tiles, cout), device=out.device, dtype=torch.float32)
-        stat_sq = torch.empty((tiles, cout), device=out.device, dtype=torch.float32)
+        stat_sum, stat_sq = _stat_buffers(n, h, w, cout, out.device)
     N.check(lib.dpb_conv3x3_gemm(mode, n, h, w, cin, cout, N.ptr(inp), N.ptr(inp2), N.ptr(weight), N.ptr(out),
-                                 N.ptr(bias), N.ptr(stat_sum), N.ptr(stat_sq), N.ptr(conv_ws),
-                                 N.ptr(conv_counters), nt, splits, ctypes.byref(m_tiles), N.stream()),
+                                 N.ptr(bias), N.ptr(stat_sum), N.ptr(stat_sq), N.ptr(conv_ws), nt, splits,
+                                 ctypes.byref(m_tiles), N.stream()),
             "dpb_conv3x3_gemm")
     N.count_launches(lib.dpb_conv_last_launches())
     if want_stats:
         return stat_sum, stat_sq, m_tiles.value
     return None
+
+
+def _stat_buffers(n: int, h: int, w: int, cout: int, device):
+    tiles = (n * h * w + 127) // 128
+    tiles *= 32 if tiles <= 64 else 4  # split-K leaves up to 32 (<= 64 tiles) / 4 partial rows per tile, else 1
+    return (torch.empty((tiles, cout), device=device, dtype=torch.float32),
+            torch.empty((tiles, cout), device=device, dtype=torch.float32))
+
+
+def conv3x3_fprop_bn(n: int, h: int, w: int, cin: int, cout: int, x: torch.Tensor, weight: torch.Tensor,
+                     y: torch.Tensor, bias, gamma, beta, running_mean, running_var, nbt, momentum: float, eps: float,
+                     nt: int = 0, splits: int = 0) -> torch.Tensor:
+    """Conv fprop + training-mode BatchNorm statistics; returns stats = (4, C): scale, shift, mean, invstd.  The
+    finalize runs inside the conv (or split-K reduce) kernel whenever the partial rows are few enough."""
+    lib = N.require()
+    sc = scratch(y.device)
+    stat_sum, stat_sq = _stat_buffers(n, h, w, cout, y.device)
+    stats = torch.empty((4, cout), device=y.device, dtype=torch.float32)
+    N.check(lib.dpb_conv3x3_fprop_bn(n, h, w, cin, cout, N.ptr(x), N.ptr(weight), N.ptr(y), N.ptr(bias),
+                                     N.ptr(stat_sum), N.ptr(stat_sq), N.ptr(sc.conv_ws), N.ptr(sc.conv_counters),
+                                     N.ptr(gamma), N.ptr(beta), N.ptr(running_mean), N.ptr(running_var), N.ptr(nbt),
+                                     momentum, eps, N.ptr(stats), nt, splits, N.stream()), "dpb_conv3x3_fprop_bn")
+    N.count_launches(lib.dpb_conv_last_launches())
+    return stats
 
 
 def first_conv_fprop(x_nchw: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], y: torch.Tensor,
@@ -183,6 +207,24 @@ def first_conv_fprop(x_nchw: torch.Tensor, weight: torch.Tensor, bias: Optional[
                                      w, N.stream()), "dpb_first_conv_fprop")
     N.count_launches(1)
     return ps, pq, blocks
+
+
+def first_conv_fprop_bn(x_nchw: torch.Tensor, weight: torch.Tensor, bias, y: torch.Tensor, gamma, beta, running_mean,
+                        running_var, nbt, momentum: float, eps: float) -> torch.Tensor:
+    """First layer + BatchNorm statistics (finalize folded into the kernel's last block); returns stats (4, 64)."""
+    lib = N.require()
+    n, _, h, w = x_nchw.shape
+    sc = scratch(y.device)
+    blocks = lib.dpb_first_conv_blocks(n, h, w)
+    ps = torch.empty((blocks, 64), device=y.device, dtype=torch.float32)
+    pq = torch.empty((blocks, 64), device=y.device, dtype=torch.float32)
+    stats = torch.empty((4, 64), device=y.device, dtype=torch.float32)
+    N.check(lib.dpb_first_conv_fprop_bn(N.ptr(x_nchw), N.ptr(weight), N.ptr(bias), N.ptr(y), N.ptr(ps), N.ptr(pq), n, h,
+                                        w, N.ptr(sc.conv_counters), N.ptr(gamma), N.ptr(beta), N.ptr(running_mean),
+                                        N.ptr(running_var), N.ptr(nbt), momentum, eps, N.ptr(stats), N.stream()),
+            "dpb_first_conv_fprop_bn")
+    N.count_launches(lib.dpb_conv_last_launches())
+    return stats
 
 
 def first_conv_wgrad(x_nchw: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor):
@@ -233,10 +275,10 @@ def bn_relu_pool_bwd(y, dout, stats, gamma, dgamma, dbeta, conv_dbias, pool: boo
     dy = torch.empty_like(y)
     N.check(lib.dpb_bn_relu_pool_bwd(N.ptr(y), N.ptr(dout), N.ptr(stats[0]), N.ptr(stats[1]), N.ptr(stats[2]),
                                      N.ptr(stats[3]), N.ptr(gamma), N.ptr(sc.bn_part), N.ptr(sc.bn_coef),
-                                     N.ptr(dgamma), N.ptr(dbeta), N.ptr(conv_dbias), N.ptr(dy), n, h, w, c, int(pool),
-                                     N.stream()),
+                                     N.ptr(sc.bn_counters), N.ptr(dgamma), N.ptr(dbeta), N.ptr(conv_dbias), N.ptr(dy),
+                                     n, h, w, c, int(pool), N.stream()),
             "dpb_bn_relu_pool_bwd")
-    N.count_launches(lib.dpb_bn_bwd_launches(n, h, w, c, int(pool)))
+    N.count_launches(lib.dpb_bn_bwd_launches(c, 1))
     return dy
 
 
@@ -357,6 +399,55 @@ def cross_entropy_bwd(logits, target, grad_out) -> torch.Tensor:
             "dpb_cross_entropy_bwd")
     N.count_launches(1)
     return dz
+
+
+def head_supported(k: int, o: int) -> bool:
+    return bool(N.require().dpb_head_supported(k, o))
+
+
+def head_fwd(x, w, b, target, metrics=None, want_dz: bool = True):
+    """Linear + mean cross-entropy (+ dz = dLoss/dlogits for a unit upstream gradient) in ONE launch.
+    Returns (loss, logits, dz)."""
+    lib = N.require()
+    bsz, k = x.shape
+    o = w.shape[0]
+    sc = scratch(x.device)
+    logits = torch.empty((bsz, o), device=x.device, dtype=torch.float32)
+    dz = torch.empty((bsz, o), device=x.device, dtype=torch.float32) if want_dz else None
+    terms = torch.empty((bsz, 2), device=x.device, dtype=torch.float32)
+    loss = torch.empty((), device=x.device, dtype=torch.float32)
+    N.check(lib.dpb_head_fwd(N.ptr(x), N.ptr(w), N.ptr(b), N.ptr(target), N.ptr(logits), N.ptr(dz), N.ptr(terms),
+                             N.ptr(loss), N.ptr(metrics), N.ptr(sc.head_counter), bsz, k, o, N.stream()), "dpb_head_fwd")
+    N.count_launches(1)
+    return loss, logits, dz
+
+
+def head_bwd(dz, x, w, grad_out, dx, dw, db) -> None:
+    lib = N.require()
+    bsz, k = x.shape
+    o = w.shape[0]
+    N.check(lib.dpb_head_bwd(N.ptr(dz), N.ptr(x), N.ptr(w), N.ptr(grad_out), N.ptr(dx), N.ptr(dw), N.ptr(db), bsz, k, o,
+                             N.stream()), "dpb_head_bwd")
+    N.count_launches(1)
+
+
+def augment_batch(images_u8: torch.Tensor, labels: torch.Tensor, indices: torch.Tensor, train: bool, seed: int,
+                  epoch: int, draws: Optional[torch.Tensor] = None):
+    """One launch: gather + RandomCrop(pad 4) + flip + Normalize on the device.  images_u8: (N, 3, H, W) uint8 on the
+    GPU, indices: int32 device tensor.  Returns (x fp32 NCHW, y int64)."""
+    from ..data.datasets import CIFAR_MEAN, CIFAR_STD
+    lib = N.require()
+    b = indices.numel()
+    _, _, h, w = images_u8.shape
+    x = torch.empty((b, 3, h, w), device=images_u8.device, dtype=torch.float32)
+    y = torch.empty((b,), device=images_u8.device, dtype=torch.int64)
+    inv = (1.0 / torch.tensor(CIFAR_STD, dtype=torch.float32)).tolist()  # the same rounding as the host transform
+    mean = torch.tensor(CIFAR_MEAN, dtype=torch.float32).tolist()
+    N.check(lib.dpb_augment_batch(N.ptr(images_u8), N.ptr(labels), N.ptr(indices), b, h, w, int(train),
+                                  seed & 0xFFFFFFFF, epoch & 0xFFFFFFFF, N.ptr(draws), mean[0], mean[1], mean[2],
+                                  inv[0], inv[1], inv[2], N.ptr(x), N.ptr(y), N.stream()), "dpb_augment_batch")
+    N.count_launches(1)
+    return x, y
 
 
 def sgd_step(p, g, m, n: int, lr: float, momentum: float, wd: float, grad_scale: float = 1.0,

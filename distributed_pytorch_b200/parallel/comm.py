@@ -11,10 +11,27 @@ rendezvous, same ``--master-ip`` and port): it is used once, to exchange CUDA IP
 
 ``Communicator.emulated(n)`` builds an n-rank world inside ONE process on ONE GPU (n buffers, n pads, cooperative
 launch with the rank in ``blockIdx.y``): that is how the collective kernels are unit-tested on a single B200.
+
+Two ways of sharing device memory between the ranks' processes:
+
+* **VMM** (default where the driver offers it): ``cuMemCreate`` allocations exported as POSIX file descriptors, which the
+  ranks pass to one another over unix sockets (:class:`_FdExchanger`).  Such memory can be bound to an NVSwitch
+  *multicast object*; buffers allocated with ``multicast=True`` then carry a second address (``mc_ptr``) through which
+  ``multimem`` instructions reduce and broadcast inside the switch (the NVLS all-reduce).
+* **CUDA IPC** (``DPB_SYMM=ipc`` or when VMM is unavailable): ``cudaIpcGetMemHandle`` / ``cudaIpcOpenMemHandle``;
+  plain peer loads and stores only.
+
+All ranks of a communicator must live on one host whose GPUs can address each other (NVLink / NVSwitch): the data plane
+is peer memory, not a network.  The constructor checks this and says so, instead of failing inside a CUDA call.
 """
 from __future__ import annotations
 
 import ctypes
+import os
+import socket
+import struct
+import tempfile
+import uuid
 from typing import List, Optional, Sequence
 
 import torch
@@ -37,14 +54,83 @@ def _wrap(ptr: int, numel: int, device: torch.device) -> torch.Tensor:
     return torch.as_tensor(_CudaArray(ptr, numel), device=device)
 
 
+class _FdExchanger:
+    """Passes file descriptors between the ranks of one host (SCM_RIGHTS over unix stream sockets).  Every rank listens
+    on its own socket; the paths are agreed over torch.distributed once."""
+
+    def __init__(self, comm: "Communicator"):
+        self.rank, self.world = comm.rank, comm.world_size
+        tag = comm.exchange(uuid.uuid4().hex.encode())[0].decode()  # rank 0's tag names the job
+        self.paths = [os.path.join(tempfile.gettempdir(), f"dpb200_{tag}_{r}.sock") for r in range(self.world)]
+        self.sock = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        if os.path.exists(self.paths[self.rank]):
+            os.unlink(self.paths[self.rank])
+        self.sock.bind(self.paths[self.rank])
+        self.sock.listen(self.world + 4)
+        self.sock.settimeout(120)
+        self.seq = 0
+        comm.host_barrier()  # everybody listens before anybody connects
+
+    def _send(self, dst: int, fd: int) -> None:
+        with socket.socket(socket.AF_UNIX, socket.SOCK_STREAM) as s:
+            s.connect(self.paths[dst])
+            socket.send_fds(s, [struct.pack("ii", self.seq, self.rank)], [fd])
+
+    def _recv(self):
+        conn, _ = self.sock.accept()
+        with conn:
+            msg, fds, _, _ = socket.recv_fds(conn, 8, 1)
+        seq, src = struct.unpack("ii", msg)
+        if seq != self.seq or len(fds) != 1:
+            raise RuntimeError(f"fd exchange out of step: got message {seq} from rank {src}, expected {self.seq}")
+        return src, fds[0]
+
+    def all_gather(self, fd: int) -> List[int]:
+        """Every rank's descriptor, as descriptors of this process (own entry: ``fd`` itself)."""
+        self.seq += 1
+        for r in range(self.world):
+            if r != self.rank:
+                self._send(r, fd)
+        out = [-1] * self.world
+        out[self.rank] = fd
+        for _ in range(self.world - 1):
+            src, f = self._recv()
+            out[src] = f
+        return out
+
+    def broadcast(self, fd: Optional[int], root: int = 0) -> int:
+        self.seq += 1
+        if self.rank == root:
+            for r in range(self.world):
+                if r != root:
+                    self._send(r, fd)
+            return fd
+        return self._recv()[1]
+
+    def close(self) -> None:
+        try:
+            self.sock.close()
+            os.unlink(self.paths[self.rank])
+        except OSError:
+            pass
+
+
 class SymmetricBuffer:
-    def __init__(self, comm: "Communicator", numel: int):
+    def __init__(self, comm: "Communicator", numel: int, multicast: bool = False):
         lib = N.require()
         self.comm = comm
         self.numel = int(numel)
         nbytes = 4 * self.numel
         self._local_ptrs: List[int] = []   # emulated: one per virtual rank; real: just ours
         self._imported: List[int] = []
+        self._vmm: Optional[dict] = None   # VMM bookkeeping (handles, padded size) when allocated that way
+        self.mc_ptr: Optional[int] = None  # multicast view of the buffer (NVLS), if bound
+        if not comm.emulate and comm.world_size > 1 and comm.use_vmm:
+            self._alloc_vmm(nbytes, multicast)
+            self.table = (ctypes.c_void_p * len(self.peer_ptrs))(*self.peer_ptrs)
+            self.tensors = [_wrap(p, self.numel, comm.device) for p in self._local_ptrs]
+            self.tensor = self.tensors[0]
+            return
         nlocal = comm.world_size if comm.emulate else 1
         for _ in range(nlocal):
             p = ctypes.c_void_p()
@@ -71,8 +157,81 @@ class SymmetricBuffer:
         self.tensors = [_wrap(p, self.numel, comm.device) for p in self._local_ptrs]
         self.tensor = self.tensors[comm.rank if comm.emulate else 0]
 
+    # ------------------------------------------------------------------------------------------------ VMM / multicast
+    def _alloc_vmm(self, nbytes: int, multicast: bool) -> None:
+        lib = N.require()
+        comm = self.comm
+        gran = comm.vmm_gran
+        padded = (nbytes + gran - 1) // gran * gran
+        ptr, handle, fd = ctypes.c_void_p(), ctypes.c_ulonglong(), ctypes.c_int(-1)
+        N.check(lib.dpb_vmm_alloc(padded, gran, ctypes.byref(ptr), ctypes.byref(handle), ctypes.byref(fd)), "dpb_vmm_alloc")
+        self._local_ptrs = [ptr.value]
+        self._vmm = {"padded": padded, "handle": handle.value, "peers": [], "mc_handle": 0}
+        fds = comm.fds.all_gather(fd.value)
+        self.peer_ptrs = []
+        for r, f in enumerate(fds):
+            if r == comm.rank:
+                self.peer_ptrs.append(ptr.value)
+                continue
+            q, h = ctypes.c_void_p(), ctypes.c_ulonglong()
+            N.check(lib.dpb_vmm_import(f, padded, gran, 1, ctypes.byref(q), ctypes.byref(h)), f"dpb_vmm_import(rank {r})")
+            os.close(f)
+            self.peer_ptrs.append(q.value)
+            self._vmm["peers"].append((q.value, h.value))
+        os.close(fd.value)
+        comm.host_barrier()
+        if multicast and comm.multicast_ok:
+            self._bind_multicast(padded, gran)
+
+    def _bind_multicast(self, padded: int, gran: int) -> None:
+        """Rank 0 creates the multicast object, every rank adds its device, then (all added) binds its memory and maps
+        the multicast view.  Any rank failing any step makes ALL ranks fall back to plain peer access."""
+        lib = N.require()
+        comm = self.comm
+        mc, mfd = ctypes.c_ulonglong(0), ctypes.c_int(-1)
+        ok = True
+        if comm.rank == 0:
+            ok = lib.dpb_mc_create(comm.world_size, padded, ctypes.byref(mc), ctypes.byref(mfd)) == 0
+        if comm.exchange(b"1" if ok else b"0")[0] != b"1":  # rank 0 could not create the object: nobody goes on
+            comm.multicast_error = "cuMulticastCreate failed on rank 0"
+            return
+        f = comm.fds.broadcast(mfd.value if comm.rank == 0 else None, root=0)
+        if comm.rank != 0:
+            dummy = ctypes.c_void_p()
+            ok = lib.dpb_vmm_import(f, padded, gran, 0, ctypes.byref(dummy), ctypes.byref(mc)) == 0
+        os.close(f)
+        ok = ok and lib.dpb_mc_add_device(mc.value) == 0
+        everyone = all(x == b"1" for x in comm.exchange(b"1" if ok else b"0"))  # also the "all devices added" barrier
+        mptr = ctypes.c_void_p()
+        if everyone:
+            ok = lib.dpb_mc_bind_map(mc.value, self._vmm["handle"], padded, gran, ctypes.byref(mptr)) == 0
+            everyone = all(x == b"1" for x in comm.exchange(b"1" if ok else b"0"))
+        if everyone:
+            self.mc_ptr = mptr.value
+            self._vmm["mc_handle"] = mc.value
+        else:
+            if mptr.value:
+                lib.dpb_mc_unbind(mc.value, padded)
+                lib.dpb_vmm_unmap(mptr, padded, 0)
+            if mc.value:
+                lib.dpb_vmm_unmap(None, 0, mc.value)
+            comm.multicast_error = lib.dpb_last_error().decode() or "multicast set-up failed on a peer"
+
     def free(self) -> None:
         lib = N.require()
+        if self._vmm is not None:
+            v = self._vmm
+            if self.mc_ptr:
+                lib.dpb_mc_unbind(v["mc_handle"], v["padded"])
+                lib.dpb_vmm_unmap(self.mc_ptr, v["padded"], v["mc_handle"])
+                self.mc_ptr = None
+            for q, h in v["peers"]:
+                lib.dpb_vmm_unmap(q, v["padded"], h)
+            for p in self._local_ptrs:
+                lib.dpb_vmm_unmap(p, v["padded"], v["handle"])
+            self._local_ptrs = []
+            self._vmm = None
+            return
         for q in self._imported:
             lib.dpb_symm_close(q)
         self._imported = []
@@ -88,6 +247,15 @@ class Communicator:
         self._buffers: List[SymmetricBuffer] = []
         self._handle = ctypes.c_void_p()
         torch.cuda.set_device(device)
+        N.init_device(device.index)
+        self.use_vmm = False
+        self.multicast_ok = False
+        self.multicast_error: Optional[str] = None
+        self.vmm_gran = 0
+        self.fds: Optional[_FdExchanger] = None
+        if not emulate and world_size > 1:
+            self._check_topology()
+            self._pick_transport()
         pad_floats = (lib.dpb_signal_pad_bytes() + 3) // 4
         self._pad = SymmetricBuffer(self, pad_floats)
         N.check(lib.dpb_comm_create(rank, world_size, self._pad.table, int(emulate), ctypes.byref(self._handle)),
@@ -107,6 +275,45 @@ class Communicator:
         device = device or torch.device("cuda", torch.cuda.current_device())
         return cls(0, world_size, device, None, emulate=True)
 
+    # ---------------------------------------------------------------------------------------------- set-up checks
+    def _check_topology(self) -> None:
+        """The data plane is peer memory: every rank must be on this host, on its own GPU, with peer access."""
+        me = (socket.gethostname(), self.device.index if self.device.index is not None else torch.cuda.current_device())
+        import pickle
+        everyone = [pickle.loads(b) for b in self.exchange(pickle.dumps(me))]
+        hosts = sorted({h for h, _ in everyone})
+        if len(hosts) > 1:
+            raise RuntimeError(
+                f"distributed_pytorch_b200: ranks are spread over several hosts {hosts}.  The CUDA gradient-sync modes "
+                "move data through NVLink peer memory and need all ranks on ONE host (one GPU per rank); for ranks on "
+                "different machines run with --device cpu (gloo), as the reference does.")
+        devs = [d for _, d in everyone]
+        if len(set(devs)) != len(devs):
+            raise RuntimeError(f"distributed_pytorch_b200: several ranks share a GPU (device per rank: {devs}); "
+                               "start one process per GPU (LOCAL_RANK / --rank select the device)")
+        for r, d in enumerate(devs):
+            if r != self.rank and not torch.cuda.can_device_access_peer(me[1], d):
+                raise RuntimeError(f"distributed_pytorch_b200: GPU {me[1]} (rank {self.rank}) cannot access GPU {d} "
+                                   f"(rank {r}) as a peer; the CUDA sync modes need NVLink/PCIe peer access between "
+                                   "all ranks' GPUs.  Use --device cpu, or a node with NVLink.")
+
+    def _pick_transport(self) -> None:
+        """VMM + file-descriptor sharing where every rank supports it (and DPB_SYMM is not 'ipc'), else CUDA IPC."""
+        lib = N.require()
+        want = os.environ.get("DPB_SYMM", "auto").lower()
+        out = (ctypes.c_longlong * 3)()
+        ok = want != "ipc" and lib.dpb_vmm_probe(self.world_size, out) == 0 and out[0] == 1 and hasattr(socket, "send_fds")
+        mine = f"{int(ok)} {int(out[1]) if ok else 0} {int(out[2]) if ok else 0}".encode()
+        votes = [tuple(int(x) for x in b.decode().split()) for b in self.exchange(mine)]
+        self.use_vmm = all(v[0] == 1 for v in votes)
+        if want == "vmm" and not self.use_vmm:
+            raise RuntimeError("DPB_SYMM=vmm requested but the CUDA virtual-memory-management path is unavailable on "
+                               f"some rank (votes: {votes})")
+        if self.use_vmm:
+            self.vmm_gran = max(v[2] for v in votes)
+            self.multicast_ok = all(v[1] == 1 for v in votes) and os.environ.get("DPB_NVLS", "1") != "0"
+            self.fds = _FdExchanger(self)
+
     # ---------------------------------------------------------------------------------------------- control plane
     def exchange(self, payload: bytes) -> List[bytes]:
         import torch.distributed as dist
@@ -120,8 +327,10 @@ class Communicator:
         dist.barrier(group=self.group)
 
     # ---------------------------------------------------------------------------------------------- buffers
-    def alloc(self, numel: int) -> SymmetricBuffer:
-        buf = SymmetricBuffer(self, numel)
+    def alloc(self, numel: int, multicast: bool = False) -> SymmetricBuffer:
+        """``multicast=True`` additionally binds the buffer to an NVSwitch multicast object when the host offers it
+        (``buf.mc_ptr`` is then set on every rank, else None on every rank)."""
+        buf = SymmetricBuffer(self, numel, multicast)
         self._buffers.append(buf)
         return buf
 
@@ -147,6 +356,27 @@ class Communicator:
         N.check(lib.dpb_allreduce_sgd(self._handle, CH_ALLREDUCE, grads.table, params.table, mom.table, offset, count,
                                       scale, lr, momentum, wd, int(nesterov), int(write_mean), blocks, N.stream()),
                 "dpb_allreduce_sgd")
+        N.count_launches(1)
+
+    def nvls_ready(self, *bufs: SymmetricBuffer) -> bool:
+        """True if these buffers can be reduced inside the switch (all multicast-bound, NVLS not switched off)."""
+        lib = N.require()
+        return (not self.emulate and self.world_size > 1 and bool(lib.dpb_nvls_enabled())
+                and all(b is not None and b.mc_ptr for b in bufs))
+
+    def all_reduce_nvls(self, grads: SymmetricBuffer, scale: float, params: Optional[SymmetricBuffer] = None,
+                        mom: Optional[torch.Tensor] = None, lr: float = 0.0, momentum: float = 0.0, wd: float = 0.0,
+                        nesterov: bool = False, write_mean: bool = False, offset: int = 0,
+                        count: Optional[int] = None, blocks: int = 0, channel: int = CH_ALLREDUCE) -> None:
+        """Two-shot all-reduce with the reduction done in the NVSwitch (``multimem``); with ``params`` / ``mom`` the SGD
+        update is fused: each rank updates its slice locally and multicasts the new parameters."""
+        lib = N.require()
+        count = grads.numel - offset if count is None else count
+        N.check(lib.dpb_allreduce_nvls(self._handle, channel, grads.mc_ptr,
+                                       params.tensor.data_ptr() if params is not None else None,
+                                       params.mc_ptr if params is not None else None,
+                                       mom.data_ptr() if mom is not None else None, offset, count, scale, lr, momentum,
+                                       wd, int(nesterov), int(write_mean), blocks, N.stream()), "dpb_allreduce_nvls")
         N.count_launches(1)
 
     def gather_mean_scatter(self, buf: SymmetricBuffer, offset: int = 0, count: Optional[int] = None,
@@ -189,3 +419,6 @@ class Communicator:
             lib.dpb_comm_destroy(self._handle)
             self._handle = ctypes.c_void_p()
         self._pad.free()
+        if self.fds is not None:
+            self.fds.close()
+            self.fds = None

@@ -70,9 +70,166 @@ def plan_buckets(bytes_in_ready_order: List[int], first_cap: int = FIRST_BUCKET_
     return ids
 
 
+def gather_sharded_momentum(comm: Communicator, mom_buf: SymmetricBuffer, ranges) -> None:
+    """Momentum of a range lives on the rank that owns the corresponding slice of the two-shot all-reduce (slice r of
+    ``ceil(n4 / world)`` float4s); broadcast every slice from its owner."""
+    world = comm.world_size
+    if world == 1:
+        return
+    comm.barrier()
+    for lo, hi in ranges:
+        n4 = (hi - lo) // 4
+        sl = (n4 + world - 1) // world * 4
+        for r in range(world):
+            a, b = lo + r * sl, min(lo + (r + 1) * sl, hi)
+            if b > a:
+                comm.broadcast(mom_buf, a, b - a, root=r)
+
+
+class BucketReducer:
+    """Reduces contiguous ranges ("buckets") of a gradient arena on a high-priority side stream as soon as the last
+    gradient of a bucket has been produced, while backward keeps running on the main stream (the C++ ready-count
+    reducer ``dpb_reducer_*``).  With an optimizer attached the SGD update is fused into each bucket's collective (the
+    slice owner updates parameters and momentum and pushes the new parameters), so no separate optimizer pass is
+    left; with multicast-bound arenas the reduction happens inside the NVSwitch.  Used by
+    :class:`DistributedDataParallel` and by ``AllReduceSync(overlap=True)``.
+
+    The collective of a bucket uses few CTAs (``DPB_DDP_BLOCKS``, default 24): it has to fit next to the convolution
+    kernels it overlaps instead of competing with them for SM slots.
+    """
+
+    def __init__(self, comm: Communicator, arena: FlatArena, grad_buf: SymmetricBuffer, bucket_of_param: List[int],
+                 num_buckets: int, scale: float, params_buf: Optional[SymmetricBuffer] = None,
+                 mom_buf: Optional[SymmetricBuffer] = None):
+        """``bucket_of_param`` is indexed like the parameter list handed to :meth:`attach`."""
+        self.comm, self.arena, self.grad_buf = comm, arena, grad_buf
+        self.params_buf, self.mom_buf = params_buf, mom_buf
+        self.num_buckets = num_buckets
+        self.scale = scale
+        self._handle = ctypes.c_void_p()
+        self._callback_queued = False
+        self._optimizer = None
+        self._arena_pos = {id(p): pos for pos, p in enumerate(arena.params)}
+        self._bucket_of_param = bucket_of_param
+        self._params: List[torch.nn.Parameter] = []
+        self.on_finalize = None
+        self.ranges: List[tuple] = []  # (first float, one past the last float) of every bucket in the arena
+
+    def attach(self, params: List[torch.nn.Parameter], optimizer=None) -> None:
+        lib = N.require()
+        self._params = list(params)
+        n = len(self.arena.params)
+        pos_of = [self._arena_pos[id(p)] for p in self._params]
+        bucket_by_pos = [0] * n
+        for i, pos in enumerate(pos_of):
+            bucket_by_pos[pos] = self._bucket_of_param[i]
+        offs = (ctypes.c_longlong * n)(*self.arena.offsets)
+        cnts = (ctypes.c_longlong * n)(*[(x + 63) // 64 * 64 for x in self.arena.numels])
+        bks = (ctypes.c_int * n)(*bucket_by_pos)
+        N.check(lib.dpb_reducer_create(self.comm.handle, n, offs, cnts, bks, self.num_buckets, self.grad_buf.table,
+                                       self.scale, ctypes.byref(self._handle)), "dpb_reducer_create")
+        self.ranges = []
+        for b in range(self.num_buckets):
+            members = [pos for pos in range(n) if bucket_by_pos[pos] == b]
+            self.ranges.append((min(self.arena.offsets[m] for m in members),
+                                max(self.arena.offsets[m] + (self.arena.numels[m] + 63) // 64 * 64 for m in members)))
+        mc_g = self.grad_buf.mc_ptr
+        mc_p = self.params_buf.mc_ptr if self.params_buf is not None else None
+        if mc_g:
+            N.check(lib.dpb_reducer_set_multicast(
+                self._handle, mc_g, mc_p, self.params_buf.tensor.data_ptr() if self.params_buf is not None else None,
+                self.mom_buf.tensor.data_ptr() if self.mom_buf is not None else None), "dpb_reducer_set_multicast")
+        self._pos_of_param = {i: pos for i, pos in enumerate(pos_of)}
+        for i, p in enumerate(self._params):
+            if p.requires_grad:
+                p.register_post_accumulate_grad_hook(self._make_hook(i))
+        if optimizer is not None:
+            self.fuse_optimizer(optimizer)
+        self.prepare()
+
+    # ------------------------------------------------------------------------------------------------ optimizer
+    def fuse_optimizer(self, optimizer) -> None:
+        """From now on every bucket's collective also applies ``optimizer``'s SGD update to the bucket's parameters."""
+        if self.params_buf is None or self.mom_buf is None:
+            raise RuntimeError("fusing the optimizer needs symmetric parameter and momentum arenas")
+        self._optimizer = optimizer
+        self._push_hyper()
+
+    @property
+    def fuses_optimizer(self) -> bool:
+        return self._optimizer is not None
+
+    def _push_hyper(self) -> None:
+        if self._optimizer is None:
+            return
+        g = self._optimizer.param_groups[0]
+        N.check(N.require().dpb_reducer_set_sgd(self._handle, self.params_buf.table, self.mom_buf.table, g["lr"],
+                                                g["momentum"], g["weight_decay"], int(g.get("nesterov", False))),
+                "dpb_reducer_set_sgd")
+
+    # ------------------------------------------------------------------------------------------------ per iteration
+    def prepare(self) -> None:
+        N.check(N.require().dpb_reducer_prepare(self._handle), "dpb_reducer_prepare")
+
+    def _make_hook(self, i: int):
+        def hook(param):
+            self._on_grad_ready(i, param)
+        return hook
+
+    def _on_grad_ready(self, i: int, param: torch.Tensor) -> None:
+        lib = N.require()
+        if not self._callback_queued:  # first gradient of this backward pass
+            torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
+            self._callback_queued = True
+            self._push_hyper()  # the learning rate may have changed since the last step
+        pos = self._pos_of_param[i]
+        want = self.arena.grad_buf.data_ptr() + 4 * self.arena.offsets[pos]
+        if param.grad.data_ptr() != want:  # producer did not write in place: move it into the bucket memory
+            v = self.arena.grad_view(pos)
+            v.copy_(param.grad)
+            param.grad = v
+        lane = K.active_wgrad_lane(param.device)
+        if lane is not None:  # weight gradients computed on the second compute stream: the reduction waits for it too
+            N.check(lib.dpb_reducer_wait_stream(self._handle, lane.stream.cuda_stream), "dpb_reducer_wait_stream")
+        N.check(lib.dpb_reducer_mark_ready(self._handle, pos, N.stream()), "dpb_reducer_mark_ready")
+
+    def _finalize_backward(self) -> None:
+        lib = N.require()
+        self._callback_queued = False
+        launched = lib.dpb_reducer_launched(self._handle)
+        N.check(lib.dpb_reducer_finalize(self._handle, N.stream()), "dpb_reducer_finalize")
+        N.count_launches(launched)
+        if self._optimizer is not None and launched > 0:
+            self._optimizer.skip_next_step = True
+        self.prepare()  # ready counts for the next backward pass
+        if self.on_finalize is not None:
+            self.on_finalize()
+
+    def gather_momentum(self) -> None:
+        """With the fused optimizer each rank holds the momentum of its own slice of every bucket only; before a
+        checkpoint, pull every slice so ``optimizer.state_dict()`` is complete on every rank (collective)."""
+        if self._optimizer is None:
+            return
+        gather_sharded_momentum(self.comm, self.mom_buf, self.ranges)
+
+    def side_stream(self) -> int:
+        out = ctypes.c_void_p()
+        N.check(N.require().dpb_reducer_side_stream(self._handle, ctypes.byref(out)), "dpb_reducer_side_stream")
+        return out.value
+
+    def close(self) -> None:
+        if self._handle:
+            torch.cuda.synchronize()
+            N.require().dpb_reducer_destroy(self._handle)
+            self._handle = ctypes.c_void_p()
+
+
 class DistributedDataParallel(nn.Module):
     def __init__(self, module: nn.Module, bucket_cap_mb: float = DEFAULT_BUCKET_MB, broadcast_buffers: bool = True,
                  process_group=None, comm: Optional[Communicator] = None):
+        """Same call as ``torch.nn.parallel.DistributedDataParallel(model)`` (reference main_ddp.py:137).  After
+        building the optimizer, ``ddp.fuse_optimizer(optimizer)`` (CUDA) moves the SGD update into each bucket's
+        collective, which removes the separate optimizer pass from the step."""
         super().__init__()
         self.module = module
         self.process_group = process_group
@@ -94,7 +251,7 @@ class DistributedDataParallel(nn.Module):
         self.bucket_sizes = [sum(s for s, b in zip(sizes, bucket_ready) if b == k) for k in range(self.num_buckets)]
 
         self._callback_queued = False
-        self._reducer = ctypes.c_void_p()
+        self.reducer: Optional[BucketReducer] = None
         self.comm = comm
         self._owns_comm = False
         self._bufs: dict[str, SymmetricBuffer] = {}
@@ -105,9 +262,10 @@ class DistributedDataParallel(nn.Module):
             self._pending = [0] * self.num_buckets
             self._works = []
         self._sync_module_states()
-        for i, p in enumerate(self._params):
-            if p.requires_grad:
-                p.register_post_accumulate_grad_hook(self._make_hook(i))
+        if not self._cuda:
+            for i, p in enumerate(self._params):
+                if p.requires_grad:
+                    p.register_post_accumulate_grad_hook(self._make_hook(i))
 
     # ------------------------------------------------------------------------------------------------ set-up
     def _verify_shapes(self) -> None:
@@ -130,11 +288,11 @@ class DistributedDataParallel(nn.Module):
             raise RuntimeError("wrap the model in DistributedDataParallel before any other arena adoption")
 
         def allocator(numel: int, kind: str) -> torch.Tensor:
-            if kind in ("grad", "param"):
-                b = self.comm.alloc(numel)
-                self._bufs[kind] = b
-                return b.tensor
-            return torch.zeros(numel, device=dev, dtype=torch.float32)
+            # all three arenas are symmetric: gradients are reduced, parameters are broadcast at construction and pushed
+            # by the slice owner when the optimizer is fused, momentum is addressed through the same peer table
+            b = self.comm.alloc(numel, multicast=(kind != "mom"))
+            self._bufs[kind] = b
+            return b.tensor
 
         # arena laid out in gradient-ready order => every bucket is one contiguous range
         names = [n for n, _ in self.module.named_parameters()]
@@ -142,13 +300,9 @@ class DistributedDataParallel(nn.Module):
         self.arena = FlatArena([self._params[i] for i in order], [names[i] for i in order], allocator)
         self.module._dpb_arena = self.arena
         self._arena_pos = {i: pos for pos, i in enumerate(order)}
-        n = len(order)
-        offs = (ctypes.c_longlong * n)(*self.arena.offsets)
-        cnts = (ctypes.c_longlong * n)(*[(x + 63) // 64 * 64 for x in self.arena.numels])
-        bks = (ctypes.c_int * n)(*[self.bucket_of_param[i] for i in order])
-        N.check(lib.dpb_reducer_create(self.comm.handle, n, offs, cnts, bks, self.num_buckets,
-                                       self._bufs["grad"].table, 1.0 / self.world_size, ctypes.byref(self._reducer)),
-                "dpb_reducer_create")
+        self.reducer = BucketReducer(self.comm, self.arena, self._bufs["grad"], self.bucket_of_param, self.num_buckets,
+                                     1.0 / self.world_size, params_buf=self._bufs["param"], mom_buf=self._bufs["mom"])
+        self.reducer.attach(self._params)
         # BatchNorm buffers into one symmetric block: floats first, then the int64 counters
         fbufs = [(m, k, b) for m in self.module.modules() for k, b in m._buffers.items()
                  if b is not None and b.dtype == torch.float32]
@@ -198,17 +352,43 @@ class DistributedDataParallel(nn.Module):
                     dist.broadcast(b, src=0, group=self.process_group)
 
     # ------------------------------------------------------------------------------------------------ forward/backward
-    def forward(self, *args, **kwargs):
+    def _pre_forward(self) -> None:
         if self.training and torch.is_grad_enabled():
             if self.broadcast_buffers:
                 self._sync_buffers()
             self._prepare_for_backward()
+
+    def forward(self, *args, **kwargs):
+        self._pre_forward()
         return self.module(*args, **kwargs)
+
+    def forward_loss(self, x, target):
+        """Forward + fused classifier/loss of the wrapped model (see ``VGG.forward_loss``), with DDP's pre-forward
+        work (buffer broadcast, reducer reset)."""
+        self._pre_forward()
+        inner = getattr(self.module, "forward_loss", None)
+        if inner is None:
+            from ..ops import functional as Fn
+            return Fn.cross_entropy(self.module(x), target)
+        return inner(x, target)
+
+    def fuse_optimizer(self, optimizer) -> None:
+        """CUDA: apply ``optimizer``'s SGD update inside each bucket's collective (``optimizer.step()`` then only
+        publishes the state).  No-op on CPU."""
+        if self._cuda and self.world_size >= 1:
+            self.reducer.fuse_optimizer(optimizer)
+
+    @property
+    def fuses_optimizer(self) -> bool:
+        return bool(self._cuda and self.reducer is not None and self.reducer.fuses_optimizer)
+
+    def nvls(self) -> bool:
+        return bool(self._cuda and self.comm.nvls_ready(self._bufs["grad"]))
 
     def _prepare_for_backward(self) -> None:
         self._callback_queued = False
         if self._cuda:
-            N.check(N.require().dpb_reducer_prepare(self._reducer), "dpb_reducer_prepare")
+            self.reducer.prepare()
         else:
             counts = [0] * self.num_buckets
             for i, p in enumerate(self._params):
@@ -223,22 +403,10 @@ class DistributedDataParallel(nn.Module):
         return hook
 
     def _on_grad_ready(self, i: int, param: torch.Tensor) -> None:
+        # CPU (gloo) path; on CUDA the BucketReducer owns the hooks
         if not self._callback_queued:
             torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
             self._callback_queued = True
-        if self._cuda:
-            pos = self._arena_pos[i]
-            want = self.arena.grad_buf.data_ptr() + 4 * self.arena.offsets[pos]
-            if param.grad.data_ptr() != want:  # producer did not write in place: move it into the bucket memory
-                v = self.arena.grad_view(pos)
-                v.copy_(param.grad)
-                param.grad = v
-            lane = K.active_wgrad_lane(param.device)
-            if lane is not None:  # weight gradients computed on the second compute stream: the reduction waits for it too
-                N.check(N.require().dpb_reducer_wait_stream(self._reducer, lane.stream.cuda_stream),
-                        "dpb_reducer_wait_stream")
-            N.check(N.require().dpb_reducer_mark_ready(self._reducer, pos, N.stream()), "dpb_reducer_mark_ready")
-            return
         b = self.bucket_of_param[i]
         self._pending[b] -= 1
         if self._pending[b] == 0 and self.world_size > 1:
@@ -248,12 +416,6 @@ class DistributedDataParallel(nn.Module):
             self._works.append((work, flat, members))
 
     def _finalize_backward(self) -> None:
-        if self._cuda:
-            lib = N.require()
-            launched = lib.dpb_reducer_launched(self._reducer)
-            N.check(lib.dpb_reducer_finalize(self._reducer, N.stream()), "dpb_reducer_finalize")
-            N.count_launches(launched)
-            return
         for work, flat, members in self._works:
             work.wait()
             off = 0
@@ -267,9 +429,9 @@ class DistributedDataParallel(nn.Module):
     def close(self) -> None:
         if self._cuda:
             torch.cuda.synchronize()
-            if self._reducer:
-                N.require().dpb_reducer_destroy(self._reducer)
-                self._reducer = ctypes.c_void_p()
+            if self.reducer is not None:
+                self.reducer.close()
+                self.reducer = None
             if self._owns_comm and self.comm is not None:
                 self.comm.close()
                 self.comm = None

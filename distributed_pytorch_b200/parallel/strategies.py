@@ -74,8 +74,11 @@ class _ArenaSync(SyncStrategy):
                 self._owns_comm = True
 
             def allocator(numel: int, kind: str) -> torch.Tensor:
+                # gradients always live in symmetric memory; parameters too when the optimizer is fused into the
+                # collective (the slice owner pushes new parameters).  Momentum is only ever touched by its owner, but
+                # the P2P fused kernel addresses it through the same peer table, so it is symmetric as well.
                 if kind == "grad" or symmetric_params:
-                    b = self.comm.alloc(numel)
+                    b = self.comm.alloc(numel, multicast=(kind != "mom"))
                     self._bufs[kind] = b
                     return b.tensor
                 return torch.zeros(numel, device=self.comm.device, dtype=torch.float32)
@@ -86,6 +89,10 @@ class _ArenaSync(SyncStrategy):
             self.arena = adopt_module(model, allocator)
 
     def close(self) -> None:
+        red = getattr(self, "reducer", None)
+        if red is not None:
+            red.close()
+            self.reducer = None
         if self.cuda and self._owns_comm and self.comm is not None:
             self.comm.close()
             self.comm = None
@@ -118,24 +125,63 @@ class AllReduceSync(_ArenaSync):
     name = "all_reduce"
 
     def __init__(self, model, world_size=None, rank=None, comm=None, group=None, fuse_optimizer: bool = False,
-                 optimizer=None):
+                 optimizer=None, overlap: bool = False, bucket_cap_mb: float = 25.0):
+        """``fuse_optimizer``: the SGD update runs inside the collective (each rank updates its slice, pushes the new
+        parameters).  ``overlap``: instead of one collective after backward, the arena is cut into buckets (the DDP
+        rule) and each bucket is reduced on a side stream as soon as its last gradient exists, while backward goes on
+        -- nothing in the reference's loop (main_all_reduce.py:45-48) depends on the order in which parameters are
+        reduced, only on the result."""
         super().__init__(model, world_size, rank, comm, group, symmetric_params=fuse_optimizer)
         self.fuses_optimizer = bool(fuse_optimizer and self.cuda)
         self.optimizer = optimizer
         if self.fuses_optimizer and optimizer is None:
             raise ValueError("fuse_optimizer=True needs the optimizer")
+        self.reducer = None
+        if overlap and self.cuda and self.world_size > 1:
+            from .ddp import BucketReducer, expected_ready_order, plan_buckets
+            params = list(model.parameters())
+            ready = expected_ready_order(model)
+            ids_ready = plan_buckets([params[i].numel() * 4 for i in ready], 1024 * 1024, int(bucket_cap_mb * 1024 * 1024))
+            bucket_of = [0] * len(params)
+            for pos, i in enumerate(ready):
+                bucket_of[i] = ids_ready[pos]
+            # the arena is in named_parameters() order: a bucket (consecutive layers) is still one contiguous range
+            self.reducer = BucketReducer(self.comm, self.arena, self._bufs["grad"], bucket_of, max(ids_ready) + 1,
+                                         1.0 / self.world_size, params_buf=self._bufs.get("param"),
+                                         mom_buf=self._bufs.get("mom"))
+            self.reducer.attach(params, optimizer if self.fuses_optimizer else None)
+
+    def nvls(self) -> bool:
+        """True if the collective runs inside the NVSwitch (multicast-bound arenas)."""
+        if not self.cuda:
+            return False
+        need = [self._bufs["grad"]] + ([self._bufs["param"]] if self.fuses_optimizer else [])
+        return self.comm.nvls_ready(*need)
 
     def sync(self) -> None:
         if self.cuda:
+            if self.reducer is not None:
+                # buckets were launched from the gradient hooks during backward; the end-of-backward callback has
+                # already made this stream wait for them
+                if self.fuses_optimizer:
+                    self.optimizer.skip_next_step = True
+                return
             self.arena.ensure_grads_in_place()
+            scale = 1.0 / self.world_size
             if self.fuses_optimizer:
                 g = self.optimizer.param_groups[0]
-                self.comm.all_reduce_sgd(self._bufs["grad"], self._bufs["param"], self._bufs["mom"],
-                                         1.0 / self.world_size, g["lr"], g["momentum"], g["weight_decay"],
-                                         g["nesterov"], write_mean=False)
+                if self.nvls():
+                    self.comm.all_reduce_nvls(self._bufs["grad"], scale, self._bufs["param"], self._bufs["mom"].tensor,
+                                              g["lr"], g["momentum"], g["weight_decay"], g["nesterov"])
+                else:
+                    self.comm.all_reduce_sgd(self._bufs["grad"], self._bufs["param"], self._bufs["mom"], scale,
+                                             g["lr"], g["momentum"], g["weight_decay"], g["nesterov"],
+                                             write_mean=False)
                 self.optimizer.skip_next_step = True
+            elif self.nvls():
+                self.comm.all_reduce_nvls(self._bufs["grad"], scale)
             else:
-                self.comm.all_reduce(self._bufs["grad"], 0, self.arena.total, 1.0 / self.world_size)
+                self.comm.all_reduce(self._bufs["grad"], 0, self.arena.total, scale)
             return
         # CPU oracle: reference main_all_reduce.py:45-48
         for _, p in self.model.named_parameters():
@@ -148,11 +194,6 @@ class AllReduceSync(_ArenaSync):
         every slice so ``optimizer.state_dict()`` is complete on every rank."""
         if not self.fuses_optimizer or self.world_size == 1:
             return
-        n4 = self.arena.total // 4
-        sl = (n4 + self.world_size - 1) // self.world_size * 4
-        mom = self._bufs["mom"]
-        self.comm.barrier()
-        for r in range(self.world_size):
-            lo, hi = r * sl, min((r + 1) * sl, self.arena.total)
-            if hi > lo:
-                self.comm.broadcast(mom, lo, hi - lo, root=r)
+        from .ddp import gather_sharded_momentum
+        ranges = self.reducer.ranges if self.reducer is not None else [(0, self.arena.total)]
+        gather_sharded_momentum(self.comm, self._bufs["mom"], ranges)

@@ -21,45 +21,71 @@ extern "C" {
 typedef void* dpb_stream_t; /* cudaStream_t */
 
 /* ---- runtime ------------------------------------------------------------------------------------------------- */
-int dpb_version(void);
+int dpb_version(void); /* ABI version; the Python loader refuses a library whose version differs from its own */
 const char* dpb_last_error(void);
-/* Diagnostic left behind by a kernel that gave up (pipeline or peer-signal timeout). out[5] = code, where, block,
- * aux0, aux1.  Clears the record. */
-int dpb_last_device_error(int* out5);
-/* Bring-up aid: when buf != NULL, CTA (0,0,0) of every tensor-core conv launch copies its first pipeline stage
- * (A tile then B tile, as laid out in shared memory; up to 48 KiB) to buf. NULL switches it off. */
+/* Once per device, with that device current (dpb_comm_create does it too): registers the mapped host record that a
+ * kernel fills in before it gives up, and applies the peer-signal time-out to the device. */
+int dpb_init_device(void);
+/* Diagnostic left behind by a kernel that gave up (pipeline or peer-signal time-out).  Reads host memory only, so it
+ * works after the failed launch has left the CUDA context unusable.  device < 0 = any initialised device.
+ * out[6] = code (0 none, 1 mbarrier, 2 peer signal), where (pipeline slot / channel), block, aux0 (peer rank waited
+ * for), aux1 (epoch), rank (the waiting rank).  Clears the record. */
+int dpb_last_device_error(int device, int* out6);
+/* Bring-up aid, only in builds with -DDPB_EXPERIMENTS (tools/conv_timing.py): per-CTA trace of the conv kernel. */
 int dpb_debug_set_conv_dump(void* buf);
-/* Scratch needed by the tensor-core convolution (split-K partial tiles + arrival counters). */
+/* Scratch needed by the tensor-core convolution: split-K partial tiles of the workspace path, and the ticket counters
+ * (zero-initialised by the caller, self-resetting) of the folded BatchNorm finalize. */
 size_t dpb_conv_workspace_bytes(void);
 size_t dpb_conv_counter_bytes(void);
 
 /* ---- convolution (ref: model.py:18-23 -> aten convolution / convolution_backward) ------------------------------ */
-/* mode 0 fprop: in = X, w = W, out = Y (+bias, + per-M-tile BatchNorm partial sums if stat_sum != NULL)
+/* mode 0 fprop: in = X, w = W, out = Y (+bias, + BatchNorm partial sums if stat_sum != NULL)
  * mode 1 dgrad: in = dY, w = W, out = dX
  * mode 2 wgrad: in = dY, in2 = X, out = dW
- * nt / splits: 0 = heuristic.  m_tiles_out (optional) receives the number of rows written to stat_sum / stat_sq. */
+ * nt / splits: 0 = heuristic.  Split-K factors that are powers of two up to 16 are reduced inside the kernel by a
+ * thread-block cluster over distributed shared memory; other factors go through `workspace` and a reduce kernel.
+ * stat_rows_out (optional) receives the number of rows written to stat_sum / stat_sq (at most 32 per 128-pixel tile
+ * up to 64 tiles, 4 per tile beyond). */
 int dpb_conv3x3_gemm(int mode, int n, int h, int w, int cin, int cout, const float* in, const float* in2,
                      const float* weight, float* out, const float* bias, float* stat_sum, float* stat_sq,
-                     void* workspace, void* counters, int nt, int splits, int* m_tiles_out, dpb_stream_t stream);
+                     void* workspace, int nt, int splits, int* stat_rows_out, dpb_stream_t stream);
+/* fprop + training-mode BatchNorm statistics: y = conv(x) + bias, then stats4 = [scale | shift | mean | invstd] ([4][cout])
+ * and the running statistics / num_batches_tracked update.  The finalize runs inside the conv (or reduce) kernel, in
+ * the block that delivers the last partial row; `counters` = dpb_conv_counter_bytes() of zeroed device memory.
+ * (ref: model.py:18-24) */
+int dpb_conv3x3_fprop_bn(int n, int h, int w, int cin, int cout, const float* x, const float* weight, float* y,
+                         const float* bias, float* stat_sum, float* stat_sq, void* workspace, void* counters,
+                         const float* gamma, const float* beta, float* running_mean, float* running_var,
+                         long long* num_batches_tracked, float momentum, float eps, float* stats4, int nt, int splits,
+                         dpb_stream_t stream);
 /* Heuristic knobs (the Python loader also reads them from the environment variable in brackets).
  *  0 [DPB_CONV_TARGET_CTAS]  CTA count the split-K heuristic aims for (default 296 = two per SM)
  *  1 [DPB_CONV_NT]           preferred N tile (64 / 128 / 256, default 128) when it divides the GEMM N extent
  *  2 [DPB_COMM_BLOCKS]       default grid cap of the collective kernels (default 64, at most 128)
  *  3 [DPB_CONV_MIN_K_ITERS]  K iterations (of 32) a split must keep (default 8)
  *  4 [DPB_PDL]               programmatic dependent launch on every compute kernel (default 0)
- *  5 [DPB_CONV_CLUSTER]      TMA multicast of the B tile over a 1 / 2 / 4-CTA cluster (default 1 = none)
- *  6 [DPB_CONV_PAIR]         cta_group::2 CTA pairs, M = 256 MMAs (default 0)
+ *  5 [DPB_CONV_CLUSTER_MAX]  largest split-K factor reduced over distributed shared memory (1 = never, default 16)
  *  7 [DPB_FIRST_TC]          first (Cin = 3) layer on the tensor cores when the image tiles into 128 pixels (default 1)
- *  8 [DPB_PAIR_REDUCE]       finish two-way split-K inside the GEMM kernel instead of the reduce kernel (default 0)
- *  9 [DPB_TAIL_MAX_PIXELS]   BatchNorm backward as one cluster kernel for layers up to this many pixels (default 0 = off)
- * Defaults are the measured optimum on B200; returns non-zero for an unknown key / bad value. */
+ *  8 [DPB_BN_FOLD]           BatchNorm finalize steps folded into their producers' last block (default 1)
+ * 11 [DPB_COMM_WEAK]         two-shot all-reduce payload with weak accesses (default 0)
+ * 12 [DPB_PEER_TIMEOUT_MS]   wall-clock budget of a peer-signal wait (default 120000)
+ * 13 [DPB_DDP_BLOCKS]        grid of a per-bucket collective launched next to backward (default 24)
+ * 14 [DPB_NVLS]              in-switch (multimem) all-reduce when the buffers are multicast-bound (default 1)
+ * 15 [DPB_NVLS_BLOCKS]       its grid (default 32)
+ * Returns non-zero for an unknown key / bad value. */
 int dpb_set_tuning(int key, int value);
-/* Kernels launched by the calling thread's most recent dpb_conv3x3_gemm (1, or 2 when split-K adds its reduce). */
+/* Kernels launched by the calling thread's most recent dpb_conv3x3_gemm / dpb_conv3x3_fprop_bn /
+ * dpb_first_conv_fprop_bn (1, 2 when split-K adds its reduce or the finalize is a launch of its own, ...). */
 int dpb_conv_last_launches(void);
 /* First layer (Cin = 3, Cout = 64): x is NCHW.  part_* : [dpb_first_conv_blocks(n,h,w)][64]. */
 int dpb_first_conv_blocks(int n, int h, int w);
 int dpb_first_conv_fprop(const float* x_nchw, const float* weight, const float* bias, float* y, float* part_sum,
                          float* part_sq, int n, int h, int w, dpb_stream_t stream);
+/* ... with the BatchNorm finalize folded in (see dpb_conv3x3_fprop_bn). */
+int dpb_first_conv_fprop_bn(const float* x_nchw, const float* weight, const float* bias, float* y, float* part_sum,
+                            float* part_sq, int n, int h, int w, void* counters, const float* gamma, const float* beta,
+                            float* running_mean, float* running_var, long long* num_batches_tracked, float momentum,
+                            float eps, float* stats4, dpb_stream_t stream);
 /* partials: [dpb_first_conv_wgrad_blocks()][1728] scratch; dw: [64][3][3][3]. */
 int dpb_first_conv_wgrad_blocks(void);
 int dpb_first_conv_wgrad(const float* x_nchw, const float* dy, float* partials, float* dw, int n, int h, int w,
@@ -75,15 +101,17 @@ int dpb_bn_eval_scale_shift(int c, const float* gamma, const float* beta, const 
 int dpb_bn_relu_pool_fwd(const float* y, const float* scale, const float* shift, float* out, int n, int h, int w,
                          int c, int pool, dpb_stream_t stream);
 /* Backward of the fused block.  part: scratch [2][dpb_bn_bwd_blocks()][c]; coef: scratch [3][c].
+ * counters: 32 zeroed uint32 (self-resetting) -- with them (and c a multiple of 32) the reduction and the finalize are
+ * ONE launch (the block that delivers a channel group's last partial row finishes the group), then the apply pass;
+ * NULL keeps the three separate launches.
  * conv_dbias (optional): gradient of the preceding conv's bias, exactly zero under training-mode BatchNorm. */
 int dpb_bn_bwd_blocks(void);
-/* Kernels dpb_bn_relu_pool_bwd launches for this shape: 1 when the layer is small enough for the cluster kernel (a
- * cluster of 8 CTAs per 32 channels exchanges the per-channel sums through distributed shared memory), else 3. */
-int dpb_bn_bwd_launches(int n, int h, int w, int c, int pool);
+/* Kernels dpb_bn_relu_pool_bwd launches: 2 with counters and c % 32 == 0, else 3. */
+int dpb_bn_bwd_launches(int c, int with_counters);
 int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, const float* shift,
                          const float* save_mean, const float* save_invstd, const float* gamma, float* part,
-                         float* coef, float* dgamma, float* dbeta, float* conv_dbias, float* dy, int n, int h, int w,
-                         int c, int pool, dpb_stream_t stream);
+                         float* coef, void* counters, float* dgamma, float* dbeta, float* conv_dbias, float* dy, int n,
+                         int h, int w, int c, int pool, dpb_stream_t stream);
 
 /* ---- The same layer types on their own (ref: model.py:16-25, any arrangement other than conv->bn->relu[->pool]) ---- */
 int dpb_relu_fwd(const float* x, float* y, long long n, dpb_stream_t stream);
@@ -134,6 +162,24 @@ int dpb_cross_entropy_fwd(const float* logits, const long long* target, float* l
                           dpb_stream_t stream);
 int dpb_cross_entropy_bwd(const float* logits, const long long* target, const float* grad_out, float* dz, int b,
                           int o, dpb_stream_t stream);
+/* The whole training head in two launches (ref: model.py:40,45 + main.py:34-35).  dpb_head_fwd: logits = x W^T + b,
+ * mean cross-entropy -> loss[0] (and metrics[0] += loss, metrics[1] += arg-max hits if metrics != NULL),
+ * dz = (softmax - onehot) / b (optional).  terms: scratch [b][2]; counter: one zeroed uint32 (self-resetting).
+ * dpb_head_bwd: dx = g dz W, dw = g dz^T x, db = g sum dz with g = grad_out[0] (device scalar, NULL = 1). */
+int dpb_head_supported(int k, int o);
+int dpb_head_fwd(const float* x, const float* w, const float* bias, const long long* target, float* logits, float* dz,
+                 float* terms, float* loss, float* metrics, void* counter, int b, int k, int o, dpb_stream_t stream);
+int dpb_head_bwd(const float* dz, const float* x, const float* w, const float* grad_out, float* dx, float* dw,
+                 float* db, int b, int k, int o, dpb_stream_t stream);
+
+/* ---- input pipeline (ref: main.py:71-90 torchvision transforms + DataLoader workers) ------------------------------ */
+/* One launch per batch: gather `b` images (uint8 [N][3][h][w], resident on the device) by `indices`, apply
+ * RandomCrop(pad 4) + horizontal flip (train != 0; the draws are a hash of seed, epoch and the dataset index, or taken
+ * from `draws` = [b][3] int32 dx, dy, flip when given) and Normalize, write fp32 NCHW + int64 labels. */
+int dpb_augment_batch(const unsigned char* images, const long long* labels, const int* indices, int b, int h, int w,
+                      int train, unsigned int seed, unsigned int epoch, const int* draws, float mean0, float mean1,
+                      float mean2, float inv_std0, float inv_std1, float inv_std2, float* out_x, long long* out_y,
+                      dpb_stream_t stream);
 
 /* ---- optimizer (ref: main.py:36,103-104 torch.optim.SGD) --------------------------------------------------------- */
 int dpb_sgd_step(float* p, const float* g, float* m, long long n, float lr, float momentum, float wd,
@@ -146,12 +192,29 @@ int dpb_symm_export(void* ptr, unsigned char handle64[64]);
 int dpb_symm_import(const unsigned char handle64[64], void** peer_ptr);
 int dpb_symm_close(void* peer_ptr);
 size_t dpb_signal_pad_bytes(void);
+/* The same through the CUDA virtual-memory-management API, which is what an NVSwitch multicast object can be bound to.
+ * The ranks exchange the POSIX file descriptors themselves (unix socket, see parallel/comm.py).
+ * dpb_vmm_probe: out3 = {VMM + fd handles supported, multicast supported, granularity in bytes}.
+ * dpb_vmm_alloc: bytes (a multiple of the granularity) of zeroed device memory, mapped; handle + exportable fd.
+ * dpb_vmm_import: a peer's allocation (map = 1) or a multicast object (map = 0) from its fd.
+ * dpb_mc_*: rank 0 creates the multicast object, every rank adds its device, then -- after a barrier -- binds its
+ * memory and maps the multicast view (dpb_mc_bind_map). */
+int dpb_vmm_probe(int ndev, long long* out3);
+int dpb_vmm_alloc(size_t bytes, size_t gran, void** ptr, unsigned long long* handle, int* fd);
+int dpb_vmm_import(int fd, size_t bytes, size_t gran, int map, void** ptr, unsigned long long* handle);
+int dpb_vmm_unmap(void* ptr, size_t bytes, unsigned long long handle);
+int dpb_mc_create(int ndev, size_t bytes, unsigned long long* handle, int* fd);
+int dpb_mc_add_device(unsigned long long mc);
+int dpb_mc_bind_map(unsigned long long mc, unsigned long long mem, size_t bytes, size_t gran, void** mc_ptr);
+int dpb_mc_unbind(unsigned long long mc, size_t bytes);
 
 /* Communicator: rank, world size and every rank's signal pad. emulate = 1 runs all ranks as blockIdx.y of one
  * cooperative launch on a single GPU (tests). */
 typedef struct dpb_comm dpb_comm;
 int dpb_comm_create(int rank, int nranks, void* const* signal_pads, int emulate, dpb_comm** out);
 int dpb_comm_destroy(dpb_comm* c);
+/* Test hook (emulated worlds): virtual rank `rank` never signals, so its peers run into the peer-signal time-out. */
+int dpb_comm_debug_withhold(dpb_comm* c, int rank);
 
 /* bufs[r] = rank r's mapping of the symmetric buffer; offset/count in floats (multiples of 4).
  * algo: 0 auto, 1 one-shot, 2 two-shot.  (ref: main_all_reduce.py:45-48) */
@@ -162,6 +225,13 @@ int dpb_allreduce(dpb_comm* c, int channel, void* const* bufs, long long offset,
 int dpb_allreduce_sgd(dpb_comm* c, int channel, void* const* grads, void* const* params, void* const* momentum,
                       long long offset, long long count, float scale, float lr, float mom, float wd, int nesterov,
                       int write_mean, int blocks, dpb_stream_t stream);
+/* The same collective reduced inside the NVSwitch (multimem.ld_reduce / multimem.st): mc_grads / mc_params are the
+ * multicast views of the gradient / parameter arenas (dpb_mc_bind_map); local_params / local_mom non-NULL fuse the SGD
+ * update as above.  Real multi-GPU worlds only.  (ref: main_all_reduce.py:45-48) */
+int dpb_allreduce_nvls(dpb_comm* c, int channel, void* mc_grads, void* local_params, void* mc_params, void* local_mom,
+                       long long offset, long long count, float scale, float lr, float mom, float wd, int nesterov,
+                       int write_mean, int blocks, dpb_stream_t stream);
+int dpb_nvls_enabled(void);
 /* (ref: main_gather.py:42-59) */
 int dpb_gather_mean_scatter(dpb_comm* c, int channel, void* const* bufs, long long offset, long long count,
                             float scale, int root, int blocks, dpb_stream_t stream);
@@ -182,6 +252,12 @@ int dpb_reducer_create(dpb_comm* c, int nparams, const long long* offsets, const
                        const int* bucket_of_param, int nbuckets, void* const* grad_bufs, float scale,
                        dpb_reducer** out);
 int dpb_reducer_destroy(dpb_reducer* r);
+/* Fuse the optimizer into every bucket's collective (NULL param_bufs switches it off again). */
+int dpb_reducer_set_sgd(dpb_reducer* r, void* const* param_bufs, void* const* mom_bufs, float lr, float momentum,
+                        float wd, int nesterov);
+/* Multicast views of the arenas: buckets are then reduced inside the NVSwitch. */
+int dpb_reducer_set_multicast(dpb_reducer* r, void* mc_grads, void* mc_params, void* local_params, void* local_mom);
+int dpb_reducer_side_stream(dpb_reducer* r, dpb_stream_t* out);
 int dpb_reducer_prepare(dpb_reducer* r);
 /* Called from the autograd post-accumulate hook of parameter `param`; launches the bucket's all-reduce on the side
  * stream once its last gradient is ready. */
