@@ -28,6 +28,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 GLOBAL_BATCH = 256
 MODES = ("all_reduce", "gather", "ddp", "single")
+DEFAULT_OVERLAP = False  # all_reduce mode: bucketed overlap with backward (see profiles/bench_multi_gpu.md)
 
 
 def parse_args(argv=None):
@@ -44,6 +45,10 @@ def parse_args(argv=None):
                    help="ddp mode: gradient bucket size (default: the framework's, see DistributedDataParallel)")
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--no-fuse-optimizer", action="store_true")
+    p.add_argument("--overlap", choices=("auto", "on", "off"), default="auto",
+                   help="all_reduce mode: bucketed reduction on a side stream during backward (auto = the default of "
+                        "the framework for this world size)")
+    p.add_argument("--no-nvls", action="store_true", help="P2P loads/stores even where NVSwitch multicast is available")
     p.add_argument("--all-modes", action="store_true", help="also time the other sync modes (extra keys)")
     return p.parse_args(argv)
 
@@ -220,12 +225,24 @@ def make_batches(batch: int, count: int = 8, seed: int = 0):
     return out
 
 
+def _config(global_batch: int, batch: int, world: int, mode: str) -> dict:
+    """Identical keys (and, for the same command line, identical values) in both arms."""
+    return {"model": "VGG-11", "global_batch": global_batch, "per_rank_batch": batch, "seq_len": None,
+            "input": "3x32x32", "parallelism": f"dp{world}", "sync_mode": mode,
+            "optimizer": "SGD lr0.1 m0.9 wd1e-4",
+            "l2": "no explicit flush: every step streams params+grads+momentum (111 MB) plus that step's "
+                  "activations, a working set larger than the 126 MB L2"}
+
+
 # ---------------------------------------------------------------------------------------------------- our arm
 def build_ours(mode: str, rank: int, world: int, args):
     import torch
     import distributed_pytorch_b200 as dpb
     from distributed_pytorch_b200.utils.arena import adopt_module
 
+    from distributed_pytorch_b200 import _native
+    if args.no_nvls:
+        _native.require().dpb_set_tuning(14, 0)
     torch.manual_seed(1)
     dev = torch.device("cuda", torch.cuda.current_device())
     model = dpb.VGG11().to(dev)
@@ -233,10 +250,15 @@ def build_ours(mode: str, rank: int, world: int, args):
         kw = {} if args.bucket_cap_mb is None else {"bucket_cap_mb": args.bucket_cap_mb}
         model = dpb.DistributedDataParallel(model, **kw)
     opt = dpb.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    if mode == "ddp" and not args.no_fuse_optimizer:
+        model.fuse_optimizer(opt)
     if mode == "gather":
         sync = dpb.GatherScatterSync(model, world, rank)
     elif mode == "all_reduce":
-        sync = dpb.AllReduceSync(model, world, rank, fuse_optimizer=not args.no_fuse_optimizer, optimizer=opt)
+        overlap = (args.overlap == "on") or (args.overlap == "auto" and DEFAULT_OVERLAP and world > 1)
+        kw = {} if args.bucket_cap_mb is None else {"bucket_cap_mb": args.bucket_cap_mb}
+        sync = dpb.AllReduceSync(model, world, rank, fuse_optimizer=not args.no_fuse_optimizer, optimizer=opt,
+                                 overlap=overlap, **kw)
     else:
         sync = dpb.NoSync(model)
         if mode == "single":
@@ -293,12 +315,15 @@ def run_ours(args, rank, world, local):
         "higher_is_better": True, "scaling": "weak" if args.per_rank_batch else "strong", "vs_baseline": None,
         "dtype": "tf32 tensor-core inputs, fp32 accumulate/storage (the reference's cuDNN default)",
         "data": "synthetic 3x32x32 images, random-init weights (no network for CIFAR-10)", "impl": "ours",
-        "config": {"model": "VGG-11", "global_batch": global_batch, "per_rank_batch": batch, "seq_len": None,
-                   "input": "3x32x32", "parallelism": f"dp{world}", "sync_mode": args.mode,
-                   "fused_optimizer": bool(getattr(sync, "fuses_optimizer", False)),
-                   "cuda_graph": not args.no_graph, "optimizer": "SGD lr0.1 m0.9 wd1e-4",
-                   "l2": "no explicit flush: every step streams params+grads+momentum (111 MB) plus that step's "
-                         "activations, a working set larger than the 126 MB L2"},
+        "config": _config(global_batch, batch, world, args.mode),
+        "impl_notes": {"fused_optimizer": bool(getattr(sync, "fuses_optimizer", False)
+                                               or getattr(model, "fuses_optimizer", False)),
+                       "overlap": bool(getattr(sync, "reducer", None) is not None or args.mode == "ddp"),
+                       "nvls": bool((hasattr(sync, "nvls") and sync.nvls()) or (hasattr(model, "nvls") and model.nvls())),
+                       "cuda_graph": not args.no_graph,
+                       "host_sync_per_step": False,
+                       "note": "device-timed arm: graph replays back to back, loss read once at the end; the e2e arm "
+                               "copies a pinned host batch in and reads the loss every step (like the reference loop)"},
         "clocks": clocks,
         "e2e": {"value": global_batch / (e2e_ms / 1e3), "unit": "images/s", "ms_per_step": e2e_ms,
                 "h2d_bytes_per_step": x0.numel() * 4 + y0.numel() * 8, "d2h_bytes_per_step": 4,
@@ -412,10 +437,11 @@ def run_reference(args, rank, world, local):
         "higher_is_better": True, "scaling": "weak" if args.per_rank_batch else "strong", "vs_baseline": None,
         "dtype": "fp32 storage, cuDNN default (TF32 conv allowed), as the reference code runs on CUDA",
         "data": "synthetic 3x32x32 images, random-init weights", "impl": "reference",
-        "config": {"model": "VGG-11", "global_batch": global_batch, "per_rank_batch": batch, "seq_len": None,
-                   "input": "3x32x32", "parallelism": f"dp{world}", "sync_mode": args.mode,
-                   "code": f"baseline/_ref/{REF_SCRIPT[args.mode]}.py train_model() unmodified, backend=nccl, "
-                           "torch cuDNN/cuBLAS kernels, loss.item() every step as in the reference loop"},
+        "config": _config(global_batch, batch, world, args.mode),
+        "impl_notes": {"code": f"baseline/_ref/{REF_SCRIPT[args.mode]}.py train_model() unmodified, backend=nccl, "
+                               "torch cuDNN/cuBLAS kernels",
+                       "host_sync_per_step": True,
+                       "note": "the reference loop calls loss.item() every step in both arms"},
         "clocks": l1.clocks,
         "e2e": {"value": global_batch / (e2e_ms / 1e3), "unit": "images/s", "ms_per_step": e2e_ms,
                 "h2d_bytes_per_step": x0.numel() * 4 + y0.numel() * 8, "d2h_bytes_per_step": 4},

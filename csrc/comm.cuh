@@ -102,6 +102,7 @@ template <bool EMU, int NR, int U>
 __global__ void __launch_bounds__(512)
 allreduce_twoshot_kernel(CommCtx c, int channel, PeerPtrs data, long long off4, long long n4, float scale,
                          int write_mean, SgdArgs sgd, PeerPtrs params, PeerPtrs mom) {
+  DPB_TRACE(20);
   const int rank = comm_rank<EMU>(c);
   const int nr = (NR > 0) ? NR : c.nranks;
   const bool weak = (write_mean & 2) != 0;  // bit 1: weak payload accesses (dpb_set_tuning key 11), bit 0: write the mean
@@ -195,6 +196,7 @@ template <int U>
 __global__ void __launch_bounds__(512)
 allreduce_nvls_kernel(CommCtx c, int channel, float* mc_grads, long long off4, long long n4, float scale, int write_mean,
                       SgdArgs sgd, float* local_params, float* mc_params, float* local_mom) {
+  DPB_TRACE(21);
   const int rank = c.rank;
   const int nr = c.nranks;
   peer_barrier<false>(c, channel);  // every rank's gradients are final
@@ -239,6 +241,7 @@ allreduce_nvls_kernel(CommCtx c, int channel, float* mc_grads, long long off4, l
 template <bool EMU, int U>
 __global__ void __launch_bounds__(512)
 allreduce_oneshot_kernel(CommCtx c, int channel, PeerPtrs data, long long off4, long long n4, float scale) {
+  DPB_TRACE(24);
   const int rank = comm_rank<EMU>(c);
   const int nr = c.nranks;
   peer_barrier<EMU>(c, channel);
@@ -269,6 +272,7 @@ allreduce_oneshot_kernel(CommCtx c, int channel, PeerPtrs data, long long off4, 
 template <bool EMU, int U>
 __global__ void __launch_bounds__(512)
 gather_mean_scatter_kernel(CommCtx c, int channel, PeerPtrs data, long long off4, long long n4, float scale, int root) {
+  DPB_TRACE(22);
   const int rank = comm_rank<EMU>(c);
   const int nr = c.nranks;
   peer_barrier<EMU>(c, channel);  // every rank's gradients are final
@@ -301,6 +305,7 @@ gather_mean_scatter_kernel(CommCtx c, int channel, PeerPtrs data, long long off4
 template <bool EMU>
 __global__ void __launch_bounds__(512)
 broadcast_kernel(CommCtx c, int channel, PeerPtrs data, long long off4, long long n4, int root) {
+  DPB_TRACE(23);
   const int rank = comm_rank<EMU>(c);
   const int nr = c.nranks;
   peer_barrier<EMU>(c, channel);  // receivers are done with their old contents

@@ -21,16 +21,18 @@
 //     result is deterministic -- adds the bias and writes those rows of the output.  No workspace, no second kernel.
 //   * CLUSTER = false, splits > 1: every split writes its partial tile to a global workspace; splitk_reduce_kernel
 //     (next launch) sums them.  Used when a GEMM needs more splits than a cluster can hold (early-layer wgrad).
-// In both cases (and with no split at all) the kernel leaves one BatchNorm partial row (per-channel sum / sum of
-// squares) per contributing CTA, and the CTA that delivers the last row of its channel group performs the BatchNorm
-// finalize itself (bn_fold.cuh).
+// BatchNorm batch statistics: whichever CTA finishes output rows (unsplit, cluster, or the reduce kernel) adds its
+// per-channel sum / sum of squares to fixed-point integer accumulators in global memory (bn_acc.cuh) -- integer
+// addition is associative, so the totals are deterministic whatever the arrival order, and the consumer kernel
+// (bn_relu_pool_fwd) derives scale / shift from them in its prologue: no partial rows, no finalize launch.
 //
 // TMA loads in this kernel read only this GPU's memory (activations, weights and gradients of the local replica); there
 // is no cluster multicast of operand tiles.
 #pragma once
 #include <cuda.h>
+#include <type_traits>
 #include "ptx.cuh"
-#include "bn_fold.cuh"
+#include "bn_acc.cuh"
 
 namespace dpb {
 
@@ -47,11 +49,9 @@ struct ConvGemmParams {
   float* out;            // fprop: Y[pix][Cout]; dgrad: dX[pix][Cin]; wgrad: dW[Cout][9][Cin]
   long long out_ld;      // row pitch of `out` in floats
   const float* bias;     // fprop only (may be null)
-  float* stat_sum;       // fprop only: [stat rows][N_total] partial sums (may be null)
-  float* stat_sq;        // fprop only
+  unsigned long long* stat_acc;  // fprop only (may be null): BatchNorm batch statistics, [2][N_total] fixed-point
+                                 // accumulators (sum, sum of squares) that every finishing CTA adds its column sums to
   float* workspace;      // split-K partials of the workspace path: [tiles][splits][128*NT]
-  int stat_rows;         // fprop: partial rows the whole launch (+ reduce kernel) produces = T of the finalize
-  BnFoldArgs bn;         // fprop: finalize folded into the last-arriving block when bn.counters != null
 #ifdef DPB_EXPERIMENTS
   float* debug_dump;     // bring-up aid (tools/conv_timing.py): per-CTA globaltimer trace and issuer-thread cycle counts
 #endif
@@ -76,8 +76,6 @@ struct ConvGemmSmem {
   static constexpr bool kColredAliased = kStagingBytes + kColredBytes <= STAGES * kStageBytes;
   static constexpr int kColredOffset = kColredAliased ? kStagingBytes : STAGES * kStageBytes + kBarBytes;
   static constexpr int kTotal = 1024 /*align slack*/ + STAGES * kStageBytes + kBarBytes + (kColredAliased ? 0 : kColredBytes);
-  // the folded BatchNorm finalize borrows 8 KB of doubles from the (then dead) staged tile
-  static_assert(kStagingBytes >= 128 * 64, "finalize scratch must fit in the staged tile");
 };
 
 template <int MODE, int NT, int STAGES, bool CLUSTER>
@@ -88,6 +86,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   constexpr bool B_MN = (MODE != kFprop);
   using S = ConvGemmSmem<NT, STAGES>;
 
+  DPB_TRACE(1 + MODE);
   pdl_launch_dependents();  // the next kernel may start its prologue; it waits for our completion itself
 #ifdef DPB_EXPERIMENTS
   const unsigned cta_linear = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
@@ -111,7 +110,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   uint64_t* empty_bar = bars + STAGES;     // [STAGES]
   uint64_t* acc_bar = bars + 2 * STAGES;   // [1]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
-  volatile uint32_t* last_flag = tmem_slot + 1;
   float* colred = reinterpret_cast<float*>(smem + S::kColredOffset);
 
   const int warp = threadIdx.x >> 5;
@@ -254,8 +252,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   float* tile = staging + q * (32 * NT);
   const int row_base = m_tile * 128 + q * 32;
   const int tile_id = ((MODE == kWgrad ? wtap : 0) * gridDim.y + n_tile) * gridDim.x + m_tile;
-  const bool stats = MODE == kFprop && p.stat_sum != nullptr;
-  bool wrote_stat_row = false;  // this CTA contributed a BatchNorm partial row (uniform over the epilogue warps)
+  const bool stats = MODE == kFprop && p.stat_acc != nullptr;
 #ifdef DPB_EXPERIMENTS
   long long e_begin = 0, e_acc = 0;
 #endif
@@ -358,10 +355,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
               s0 += colred[(w * 2 + 0) * NT + c];
               s1 += colred[(w * 2 + 1) * NT + c];
             }
-            p.stat_sum[(size_t)m_tile * p.N_total + n_tile * NT + c] = s0;
-            p.stat_sq[(size_t)m_tile * p.N_total + n_tile * NT + c] = s1;
+            bn_acc_add(p.stat_acc + n_tile * NT + c, s0);
+            bn_acc_add(p.stat_acc + p.N_total + n_tile * NT + c, s1);
           }
-          wrote_stat_row = true;
         }
       }
     }
@@ -383,23 +379,45 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
       if (MODE == kFprop && p.bias != nullptr) bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + n_tile * NT) + chunk);
       float4 csum = make_float4(0.f, 0.f, 0.f, 0.f), csq = csum;
       float* obase = p.out + (size_t)(m_tile * 128) * p.out_ld + (size_t)(MODE == kWgrad ? wtap * p.CinW : 0) + n_tile * NT;
-      for (int r0 = 0; r0 < R; r0 += kRowsPerPass) {
-        const int trow = crank * R + r0 + rsub;     // row of the 128-row tile
-        if (r0 + rsub >= R) break;                   // R < rows per pass (S = 16 with NT = 64)
-        // address of (trow, chunk) inside a staged tile: slab = trow / 32, row in slab = trow % 32
-        const uint32_t local = smem_u32(staging + (trow >> 5) * (32 * NT) + (trow & 31) * NT + ((chunk ^ (trow & 7)) << 2));
-        float4 acc = bias4;
-        for (int s = 0; s < S_; ++s) {  // split order: deterministic
-          const float4 v = ld_dsmem_f4(mapa_u32_addr(local, (uint32_t)s));
-          acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-        }
-        if (m_tile * 128 + trow < p.M_total) {
-          *reinterpret_cast<float4*>(obase + (size_t)trow * p.out_ld + (chunk << 2)) = acc;
-          if (stats) {
-            csum.x += acc.x; csum.y += acc.y; csum.z += acc.z; csum.w += acc.w;
-            csq.x += acc.x * acc.x; csq.y += acc.y * acc.y; csq.z += acc.z * acc.z; csq.w += acc.w * acc.w;
+      // Row r of the finished tile = sum over the S staged partial tiles, in split order.  A distributed-shared-memory
+      // load costs several hundred cycles, so 16 of them are in flight per thread before the first add (a dependent
+      // load-add chain, and then one row pass at a time, made this loop the longest part of the kernel).
+      auto reduce_rows = [&](auto s_const) {
+        constexpr int SC = decltype(s_const)::value;
+        constexpr int PB = 16 / SC;  // row passes per batch
+        for (int r0 = 0; r0 < R; r0 += kRowsPerPass * PB) {
+          float4 v[PB][SC];
+          int trow[PB];
+#pragma unroll
+          for (int b = 0; b < PB; ++b) {
+            const int rr = r0 + b * kRowsPerPass + rsub;
+            trow[b] = rr < R ? crank * R + rr : -1;  // row of the 128-row tile
+            const int tr = trow[b] < 0 ? 0 : trow[b];
+            // address of (row, chunk) inside a staged tile: slab = row / 32, row in slab = row % 32
+            const uint32_t local = smem_u32(staging + (tr >> 5) * (32 * NT) + (tr & 31) * NT + ((chunk ^ (tr & 7)) << 2));
+#pragma unroll
+            for (int s = 0; s < SC; ++s) v[b][s] = ld_dsmem_f4(mapa_u32_addr(local, (uint32_t)s));
+          }
+#pragma unroll
+          for (int b = 0; b < PB; ++b) {
+            float4 acc = bias4;
+#pragma unroll
+            for (int s = 0; s < SC; ++s) { acc.x += v[b][s].x; acc.y += v[b][s].y; acc.z += v[b][s].z; acc.w += v[b][s].w; }
+            if (trow[b] >= 0 && m_tile * 128 + trow[b] < p.M_total) {
+              *reinterpret_cast<float4*>(obase + (size_t)trow[b] * p.out_ld + (chunk << 2)) = acc;
+              if (stats) {
+                csum.x += acc.x; csum.y += acc.y; csum.z += acc.z; csum.w += acc.w;
+                csq.x += acc.x * acc.x; csq.y += acc.y * acc.y; csq.z += acc.z * acc.z; csq.w += acc.w * acc.w;
+              }
+            }
           }
         }
+      };
+      switch (S_) {
+        case 2: reduce_rows(std::integral_constant<int, 2>{}); break;
+        case 4: reduce_rows(std::integral_constant<int, 4>{}); break;
+        case 8: reduce_rows(std::integral_constant<int, 8>{}); break;
+        default: reduce_rows(std::integral_constant<int, 16>{}); break;
       }
       if (stats) {
         // combine the kRowsPerPass threads that share a chunk, in rsub order; colred is [kRowsPerPass][2][NT] here
@@ -414,11 +432,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             s0 += colred[(w * 2 + 0) * NT + c];
             s1 += colred[(w * 2 + 1) * NT + c];
           }
-          const size_t prow = (size_t)m_tile * S_ + crank;
-          p.stat_sum[prow * p.N_total + n_tile * NT + c] = s0;
-          p.stat_sq[prow * p.N_total + n_tile * NT + c] = s1;
+          bn_acc_add(p.stat_acc + n_tile * NT + c, s0);
+          bn_acc_add(p.stat_acc + p.N_total + n_tile * NT + c, s1);
         }
-        wrote_stat_row = true;
       }
     }
     // no CTA may reuse or give up its shared memory while a peer is still reading it
@@ -431,14 +447,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc<NT>(tmem_acc);
-  }
-  // BatchNorm finalize by the CTA that delivered the last partial row of this channel group (n_tile).  The staged tile
-  // is dead by now (own epilogue done, and with CLUSTER every peer is past the second cluster barrier).
-  if (MODE == kFprop && epi && wrote_stat_row && p.bn.counters != nullptr) {
-    const unsigned expected = (unsigned)(gridDim.x * (CLUSTER ? p.splits : 1));
-    if (arrive_last(p.bn.counters + n_tile, expected, et, 1, 128, last_flag))
-      bn_finalize_cols(p.stat_sum, p.stat_sq, p.stat_rows, p.N_total, n_tile * NT, NT, p.bn, n_tile == 0, et, 1, 128,
-                       reinterpret_cast<double*>(staging));
   }
 #ifdef DPB_EXPERIMENTS
   if (p.debug_dump != nullptr && blockIdx.x == gridDim.x / 2 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 64) {

@@ -157,7 +157,6 @@ int launch_conv_gemm_mode(int nt, bool cluster, const CUtensorMap& mA, const CUt
 }
 
 constexpr size_t kConvWorkspaceBytes = (size_t)48 << 20;  // split-K partial tiles (workspace path)
-constexpr int kConvCounterSlots = 8192;                  // ticket counters of the folded BatchNorm finalize
 
 // Number of CTAs we aim for: two waves of single-tile CTAs on 148 SMs.
 // Tunables (dpb_set_tuning): CTA count the split-K heuristic aims for, and the N tile used when the GEMM N extent allows it.
@@ -166,21 +165,22 @@ inline int g_tune_wide_nt = 128;
 inline int g_tune_min_k_iters = 8;  // k-iterations (of 32) a split must keep; fewer, fatter splits = less reduce traffic
 // Largest split factor that is reduced inside the GEMM kernel over distributed shared memory (thread-block cluster along
 // the split axis; 16 needs the non-portable cluster size).  1 sends every split-K GEMM through the workspace + reduce
-// kernel instead.
-inline int g_tune_cluster_max = 16;
-inline int g_tune_bn_fold = 1;  // BatchNorm finalize folded into the producer's last-arriving block
+// kernel instead.  8 is the measured optimum (profiles/step_variants.md): 16-CTA clusters do not pack onto the GPCs --
+// of 256 CTAs 32 start a whole kernel-life late.
+inline int g_tune_cluster_max = 8;
 
 struct SplitPlan {
   int splits;
   bool cluster;
 };
 
-inline SplitPlan plan_splits(int tiles, int m_tiles, int k_iters, int nt, int forced) {
+inline SplitPlan plan_splits(int tiles, int m_tiles, int k_iters, int nt, int forced, int target) {
+  if (target <= 0) target = g_tune_target_ctas;
   int want = 1;
   if (forced > 0) {
     want = forced;
-  } else if (tiles < g_tune_target_ctas) {
-    want = g_tune_target_ctas / tiles;
+  } else if (tiles < target) {
+    want = target / tiles;
     int max_by_k = k_iters / g_tune_min_k_iters;  // keep a minimum amount of K per split
     if (max_by_k < 1) max_by_k = 1;
     if (want > max_by_k) want = max_by_k;
@@ -193,7 +193,6 @@ inline SplitPlan plan_splits(int tiles, int m_tiles, int k_iters, int nt, int fo
     while (s * 2 <= want && s * 2 <= g_tune_cluster_max) s *= 2;
     // heuristic choice: the power of two nearest to the wanted factor (6 -> 8, 5 -> 4), keeping >= 4 k-iterations a split
     if (forced <= 0 && want * 2 >= s * 3 && s * 2 <= g_tune_cluster_max && s * 2 * 4 <= k_iters) s *= 2;
-    if (m_tiles > 64 && s > 4) s = 4;  // BatchNorm partial rows: callers size them for 4 rows per tile beyond 64 tiles
     // forced: only an exact power of two goes to the cluster path (tests pick the path by the number they force);
     // heuristic: the cluster path unless the GEMM wants far more splits than a cluster holds (early-layer wgrad)
     const bool take = forced > 0 ? (s == want) : (want * 2 <= g_tune_cluster_max * 3);
@@ -211,23 +210,22 @@ inline SplitPlan plan_splits(int tiles, int m_tiles, int k_iters, int nt, int fo
 // mode: 0 fprop  (in = X[N,H,W,Cin], w = W[Cout,3,3,Cin], out = Y[N,H,W,Cout])
 //       1 dgrad  (in = dY[N,H,W,Cout], w = W, out = dX[N,H,W,Cin])
 //       2 wgrad  (in = dY[N,H,W,Cout], in2 = X[N,H,W,Cin], out = dW[Cout,3,3,Cin])
-// bn (fprop, optional): BatchNorm finalize arguments; *folded_out tells the caller whether the finalize ran inside
-// these launches (1) or still has to be launched over *out_stat_rows partial rows (0).
+// stat_acc (fprop, optional): [2][Cout] zeroed fixed-point accumulators that receive sum / sum of squares per channel.
+// target_ctas: CTA count the split-K heuristic aims for in this call (0 = the tuned default); a data-gradient and a
+// weight-gradient GEMM that run side by side on two streams each ask for one CTA per SM.
 inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, const float* in2, const float* w,
-                              float* out, const float* bias, float* stat_sum, float* stat_sq, float* workspace,
-                              int nt_override, int splits_override, int* out_stat_rows, const BnFoldArgs* bn,
-                              int* folded_out, cudaStream_t stream) {
+                              float* out, const float* bias, unsigned long long* stat_acc, float* workspace,
+                              int nt_override, int splits_override, int target_ctas, cudaStream_t stream) {
   if (g.cin % 32 || g.cout % 32) return set_error(-13, "conv_gemm needs Cin, Cout multiples of 32 (got %d, %d)", g.cin, g.cout);
   if (g.w > 32 || (g.w & (g.w - 1)) || (g.h & (g.h - 1))) return set_error(-13, "conv_gemm needs power-of-two H, W with W <= 32 (got %d x %d)", g.h, g.w);
   const long long pixels = (long long)g.n * g.h * g.w;
   ConvGemmParams p{};
   p.H = g.h; p.W = g.w; p.NImg = g.n; p.CinW = g.cin;
-  p.bias = bias; p.stat_sum = stat_sum; p.stat_sq = stat_sq; p.workspace = workspace;
+  p.bias = bias; p.stat_acc = stat_acc; p.workspace = workspace;
   p.out = out;
 #ifdef DPB_EXPERIMENTS
   p.debug_dump = g_conv_debug_dump;
 #endif
-  if (folded_out) *folded_out = 0;
   CUtensorMap mA, mB;
   dim3 grid;
   int nt;
@@ -246,7 +244,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
     p.out_ld = cn;
     const int m_tiles = (int)((pixels + 127) / 128);
     const int n_tiles = cn / nt;
-    const SplitPlan sp = plan_splits(m_tiles * n_tiles, m_tiles, p.k_iters, nt, splits_override);
+    const SplitPlan sp = plan_splits(m_tiles * n_tiles, m_tiles, p.k_iters, nt, splits_override, target_ctas);
     p.splits = sp.splits;
     if (!sp.cluster && sp.splits > 1 && workspace == nullptr) return set_error(-13, "conv_gemm: split-K needs a workspace");
     {
@@ -267,15 +265,6 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
       if ((rc = make_map_f32(&mB, w, 2, dims, str, box, true))) return rc;
     }
     grid = dim3(m_tiles, n_tiles, p.splits);
-    // BatchNorm partial rows written by these launches
-    p.stat_rows = sp.cluster ? m_tiles * sp.splits
-                             : (sp.splits > 1 ? splitk_pieces(m_tiles * n_tiles, m_tiles, nt) * m_tiles : m_tiles);
-    if (out_stat_rows) *out_stat_rows = p.stat_rows;
-    if (mode == kFprop && bn != nullptr && stat_sum != nullptr && bn->counters != nullptr && g_tune_bn_fold &&
-        p.stat_rows <= kBnFoldMaxRows && n_tiles <= kConvCounterSlots) {
-      p.bn = *bn;
-      if (folded_out) *folded_out = 1;
-    }
     if (mode == kFprop) return launch_conv_gemm_mode<kFprop>(nt, sp.cluster, mA, mB, p, grid, stream);
     return launch_conv_gemm_mode<kDgrad>(nt, sp.cluster, mA, mB, p, grid, stream);
   }
@@ -291,7 +280,7 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
   p.out_ld = (long long)9 * g.cin;
   const int m_tiles = (g.cout + 127) / 128;
   const int n_tiles = g.cin / nt;
-  const SplitPlan sp = plan_splits(m_tiles * n_tiles * 9, m_tiles, p.k_iters, nt, splits_override);
+  const SplitPlan sp = plan_splits(m_tiles * n_tiles * 9, m_tiles, p.k_iters, nt, splits_override, target_ctas);
   p.splits = sp.splits;
   if (!sp.cluster && sp.splits > 1 && workspace == nullptr) return set_error(-13, "conv_gemm: split-K needs a workspace");
   {
@@ -307,7 +296,6 @@ inline int conv_gemm_dispatch(int mode, const ConvGeom& g, const float* in, cons
     if ((rc = make_map_f32(&mB, in2, 4, dims, str, box, true))) return rc;
   }
   grid = dim3(m_tiles, n_tiles, 9 * p.splits);
-  if (out_stat_rows) *out_stat_rows = m_tiles;
   return launch_conv_gemm_mode<kWgrad>(nt, sp.cluster, mA, mB, p, grid, stream);
 }
 

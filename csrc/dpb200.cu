@@ -43,7 +43,7 @@ inline int grid_for(long long units, int threads, int cap) {
 
 extern "C" {
 
-int dpb_version(void) { return 200; }
+int dpb_version(void) { return 202; }
 const char* dpb_last_error(void) { return error_buffer(); }
 
 }  // extern "C"
@@ -104,6 +104,17 @@ int dpb_debug_set_conv_dump(void* buf) {
 #endif
 }
 
+int dpb_debug_set_trace(void* buf) {
+#ifdef DPB_EXPERIMENTS
+  unsigned long long* p = reinterpret_cast<unsigned long long*>(buf);
+  DPB_CUDA(cudaMemcpyToSymbol(g_dpb_trace, &p, sizeof(p)));
+  return 0;
+#else
+  (void)buf;
+  return set_error(-30, "kernel tracing is compiled out: rebuild libdpb200 with -DDPB_EXPERIMENTS");
+#endif
+}
+
 int dpb_set_tuning(int key, int value) {
   if (key == 0 && value >= 1) { g_tune_target_ctas = value; return 0; }
   if (key == 1 && (value == 64 || value == 128 || value == 256)) { g_tune_wide_nt = value; return 0; }
@@ -112,7 +123,6 @@ int dpb_set_tuning(int key, int value) {
   if (key == 4) { g_tune_use_pdl = value ? 1 : 0; return 0; }
   if (key == 5 && (value == 1 || value == 2 || value == 4 || value == 8 || value == 16)) { g_tune_cluster_max = value; return 0; }
   if (key == 7) { g_tune_first_tc = value ? 1 : 0; return 0; }
-  if (key == 8) { g_tune_bn_fold = value ? 1 : 0; return 0; }
   if (key == 11) { g_tune_comm_weak = value ? 1 : 0; return 0; }
   if (key == 12 && value >= 1) {  // peer-signal wait budget in milliseconds; applied to the current device at once
     g_peer_timeout_ns = (unsigned long long)value * 1000000ull;
@@ -127,54 +137,15 @@ int dpb_set_tuning(int key, int value) {
 int dpb_conv_last_launches(void) { return g_conv_last_launches; }
 
 size_t dpb_conv_workspace_bytes(void) { return kConvWorkspaceBytes; }
-size_t dpb_conv_counter_bytes(void) { return (size_t)kConvCounterSlots * sizeof(unsigned int); }
 
 // ------------------------------------------------------------------------------------------------ convolution
 int dpb_conv3x3_gemm(int mode, int n, int h, int w, int cin, int cout, const float* in, const float* in2,
-                     const float* weight, float* out, const float* bias, float* stat_sum, float* stat_sq,
-                     void* workspace, int nt, int splits, int* stat_rows_out, dpb_stream_t stream) {
+                     const float* weight, float* out, const float* bias, void* stat_acc, void* workspace, int nt,
+                     int splits, int target_ctas, dpb_stream_t stream) {
   if (mode < 0 || mode > 2) return set_error(-1, "dpb_conv3x3_gemm: bad mode %d", mode);
   ConvGeom g{n, h, w, cin, cout};
-  return conv_gemm_dispatch(mode, g, in, in2, weight, out, bias, stat_sum, stat_sq, (float*)workspace, nt, splits,
-                            stat_rows_out, nullptr, nullptr, S(stream));
-}
-
-static BnFoldArgs make_bn_args(const float* gamma, const float* beta, float* running_mean, float* running_var,
-                               long long* nbt, float momentum, float eps, double count, float* stats4, int c,
-                               void* counters) {
-  BnFoldArgs a{};
-  a.gamma = gamma; a.beta = beta; a.running_mean = running_mean; a.running_var = running_var;
-  a.num_batches_tracked = nbt; a.momentum = momentum; a.eps = eps; a.count = count;
-  a.scale = stats4; a.shift = stats4 + c; a.save_mean = stats4 + 2 * c; a.save_invstd = stats4 + 3 * c;
-  a.counters = reinterpret_cast<unsigned int*>(counters);
-  return a;
-}
-
-static int launch_bn_finalize(const float* ps, const float* pq, int rows, int c, const BnFoldArgs& a, cudaStream_t st) {
-  DPB_CUDA(launch_k(bn_finalize_kernel, dim3((c + kFinCh - 1) / kFinCh), dim3(kFinCh, kFinRows), 0, st, ps, pq, rows, c,
-                    a.count, a.gamma, a.beta, a.running_mean, a.running_var, a.num_batches_tracked, a.momentum, a.eps,
-                    a.scale, a.shift, a.save_mean, a.save_invstd));
-  return 0;
-}
-
-int dpb_conv3x3_fprop_bn(int n, int h, int w, int cin, int cout, const float* x, const float* weight, float* y,
-                         const float* bias, float* stat_sum, float* stat_sq, void* workspace, void* counters,
-                         const float* gamma, const float* beta, float* running_mean, float* running_var,
-                         long long* nbt, float momentum, float eps, float* stats4, int nt, int splits,
-                         dpb_stream_t stream) {
-  ConvGeom g{n, h, w, cin, cout};
-  const BnFoldArgs a = make_bn_args(gamma, beta, running_mean, running_var, nbt, momentum, eps, (double)n * h * w, stats4,
-                                    cout, counters);
-  int rows = 0, folded = 0;
-  int rc = conv_gemm_dispatch(kFprop, g, x, nullptr, weight, y, bias, stat_sum, stat_sq, (float*)workspace, nt, splits,
-                              &rows, &a, &folded, S(stream));
-  if (rc) return rc;
-  if (!folded) {
-    const int conv_launches = g_conv_last_launches;
-    if ((rc = launch_bn_finalize(stat_sum, stat_sq, rows, cout, a, S(stream)))) return rc;
-    g_conv_last_launches = conv_launches + 1;
-  }
-  return 0;
+  return conv_gemm_dispatch(mode, g, in, in2, weight, out, bias, (unsigned long long*)stat_acc, (float*)workspace, nt,
+                            splits, target_ctas, S(stream));
 }
 
 int dpb_first_conv_blocks(int n, int h, int w) {
@@ -191,42 +162,19 @@ static int first_conv_check(int w) {
   return 0;
 }
 
-static int first_conv_fprop_impl(const float* x, const float* weight, const float* bias, float* y, float* part_sum,
-                                 float* part_sq, int n, int h, int w, const BnFoldArgs& fold, cudaStream_t st) {
+int dpb_first_conv_uses_tensor_cores(int h, int w) { return (g_tune_first_tc && first_conv_tc_supported(h, w)) ? 1 : 0; }
+
+int dpb_first_conv_fprop(const float* x, const float* weight, const float* bias, float* y, float* part_sum,
+                         float* part_sq, void* stat_acc, int n, int h, int w, dpb_stream_t stream) {
   const int blocks = dpb_first_conv_blocks(n, h, w);
   if (g_tune_first_tc && first_conv_tc_supported(h, w)) {
     DPB_SET_MAX_SMEM_ONCE(first_conv_fprop_tc_kernel, FcTcSmem::kTotal);
-    DPB_CUDA(launch_k(first_conv_fprop_tc_kernel, dim3(blocks), dim3(kFcTcThreads), FcTcSmem::kTotal, st, x, weight, bias, y, part_sum, part_sq, n, h, w, fold));
+    DPB_CUDA(launch_k(first_conv_fprop_tc_kernel, dim3(blocks), dim3(kFcTcThreads), FcTcSmem::kTotal, S(stream), x, weight, bias, y, part_sum, part_sq, n, h, w, (unsigned long long*)stat_acc));
     return 0;
   }
+  if (stat_acc != nullptr) return set_error(-7, "first conv: the FP32-pipe kernel leaves partial rows, not accumulators");
   if (int rc = first_conv_check(w)) return rc;
-  DPB_CUDA(launch_k(first_conv_fprop_kernel, dim3(blocks), dim3(256), 0, st, x, weight, bias, y, part_sum, part_sq, n, h, w));
-  return 0;
-}
-
-int dpb_first_conv_fprop(const float* x, const float* weight, const float* bias, float* y, float* part_sum,
-                         float* part_sq, int n, int h, int w, dpb_stream_t stream) {
-  BnFoldArgs none{};
-  return first_conv_fprop_impl(x, weight, bias, y, part_sum, part_sq, n, h, w, none, S(stream));
-}
-
-int dpb_first_conv_fprop_bn(const float* x, const float* weight, const float* bias, float* y, float* part_sum,
-                            float* part_sq, int n, int h, int w, void* counters, const float* gamma, const float* beta,
-                            float* running_mean, float* running_var, long long* nbt, float momentum, float eps,
-                            float* stats4, dpb_stream_t stream) {
-  BnFoldArgs a = make_bn_args(gamma, beta, running_mean, running_var, nbt, momentum, eps, (double)n * h * w, stats4, 64,
-                              counters);
-  const int blocks = dpb_first_conv_blocks(n, h, w);
-  const bool fold = g_tune_bn_fold && counters != nullptr && g_tune_first_tc && first_conv_tc_supported(h, w) &&
-                    blocks <= kBnFoldMaxRows;
-  BnFoldArgs k = a;
-  if (!fold) k.counters = nullptr;
-  if (int rc = first_conv_fprop_impl(x, weight, bias, y, part_sum, part_sq, n, h, w, k, S(stream))) return rc;
-  g_conv_last_launches = 1;
-  if (!fold) {
-    if (int rc = launch_bn_finalize(part_sum, part_sq, blocks, 64, a, S(stream))) return rc;
-    g_conv_last_launches = 2;
-  }
+  DPB_CUDA(launch_k(first_conv_fprop_kernel, dim3(blocks), dim3(256), 0, S(stream), x, weight, bias, y, part_sum, part_sq, n, h, w));
   return 0;
 }
 
@@ -286,37 +234,64 @@ int dpb_bn_relu_pool_fwd(const float* y, const float* scale, const float* shift,
   return 0;
 }
 
+int dpb_bn_relu_pool_fwd_train(const float* y, void* acc, void* ticket, const float* gamma, const float* beta,
+                               float* running_mean, float* running_var, long long* nbt, float momentum, float eps,
+                               float* stats4, float* out, int n, int h, int w, int c, int pool, dpb_stream_t stream) {
+  if (c % 4 || c > kBnMaxC) return set_error(-2, "bn_relu_pool: C must be a multiple of 4 and <= %d (got %d)", kBnMaxC, c);
+  if (pool && ((h | w) & 1)) return set_error(-2, "bn_relu_pool: pooling needs even H, W (got %dx%d)", h, w);
+  BnTrainArgs a{};
+  a.acc = reinterpret_cast<unsigned long long*>(acc);
+  a.ticket = reinterpret_cast<unsigned int*>(ticket);
+  a.gamma = gamma; a.beta = beta; a.running_mean = running_mean; a.running_var = running_var;
+  a.num_batches_tracked = nbt; a.momentum = momentum; a.eps = eps; a.count = (double)n * h * w; a.stats4 = stats4;
+  const long long opix = pool ? (long long)n * (h / 2) * (w / 2) : (long long)n * h * w;
+  const long long units = opix * (c / 4);
+  // one float4 per thread up to 8 blocks per SM: the element loop is latency-bound, so it wants the loads of many
+  // threads in flight rather than a serial loop per thread; the per-block prologue (C channels) runs concurrently
+  const int blocks = grid_for(units, 256, 148 * 8);
+  if (pool) {
+    DPB_CUDA(launch_k(bn_relu_pool_fwd_acc_kernel<true>, dim3(blocks), dim3(256), 0, S(stream), y, a, out, units, c, h, w));
+  } else {
+    DPB_CUDA(launch_k(bn_relu_pool_fwd_acc_kernel<false>, dim3(blocks), dim3(256), 0, S(stream), y, a, out, units, c, h, w));
+  }
+  return 0;
+}
+
 int dpb_bn_bwd_blocks(void) { return kBnBwdBlocks; }
 
-int dpb_bn_bwd_launches(int c, int with_counters) {
-  return (with_counters && g_tune_bn_fold && c % 32 == 0) ? 2 : 3;
-}
+int dpb_bn_bwd_launches(int c, int with_acc) { return (with_acc && c % 32 == 0) ? 2 : 3; }
 
 int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, const float* shift,
                          const float* save_mean, const float* save_invstd, const float* gamma, float* part,
-                         float* coef, void* counters, float* dgamma, float* dbeta, float* conv_dbias, float* dy, int n,
-                         int h, int w, int c, int pool, dpb_stream_t stream) {
+                         float* coef, void* acc, void* ticket, float* dgamma, float* dbeta, float* conv_dbias, float* dy,
+                         int n, int h, int w, int c, int pool, dpb_stream_t stream) {
   if (c % 4 || c > 1024) return set_error(-2, "bn_relu_pool_bwd: C must be a multiple of 4 and <= 1024 (got %d)", c);
   const int c4 = c / 4;
   const long long opix = pool ? (long long)n * (h / 2) * (w / 2) : (long long)n * h * w;
   float* part_g = part;
   float* part_gx = part + (size_t)kBnBwdBlocks * c;
   const double count = (double)n * h * w;
-  if (counters != nullptr && g_tune_bn_fold && c % 32 == 0) {
-    // reduce + finalize in one launch: (C / 32) channel groups x slices, the last block of a group finishes it
+  const long long units = opix * c4;
+  if (acc != nullptr && ticket != nullptr && c % 32 == 0) {
+    // two launches: column sums into fixed-point accumulators, then the apply pass derives its coefficients from them
     const int groups = c / 32;
     long long slices = (2 * kBnBwdBlocks) / groups;  // ~4 blocks per SM in total
     const long long by_pixels = (opix + 31) / 32;
     if (slices > by_pixels) slices = by_pixels;
-    if (slices > kBnBwdBlocks) slices = kBnBwdBlocks;
     if (slices < 1) slices = 1;
-    unsigned int* cnt = reinterpret_cast<unsigned int*>(counters);
+    unsigned long long* a = reinterpret_cast<unsigned long long*>(acc);
+    unsigned int* t = reinterpret_cast<unsigned int*>(ticket);
+    const int ablocks = grid_for(units, 256, 148 * 8);
     if (pool) {
-      DPB_CUDA(launch_k(bn_bwd_reduce_fold_kernel<true>, dim3(groups, (unsigned)slices), dim3(256), 0, S(stream), y, dout, scale, shift, save_mean, save_invstd, gamma, part_g, part_gx, opix, c, h, w, count, dgamma, dbeta, conv_dbias, coef, cnt));
+      DPB_CUDA(launch_k(bn_bwd_reduce_acc_kernel<true>, dim3(groups, (unsigned)slices), dim3(256), 0, S(stream), y, dout, scale, shift, save_mean, save_invstd, a, opix, c, h, w));
+      DPB_CUDA(launch_k(bn_bwd_apply_acc_kernel<true>, dim3(ablocks), dim3(256), 0, S(stream), y, dout, scale, shift, save_mean, save_invstd, gamma, a, t, count, dgamma, dbeta, conv_dbias, dy, units, c, h, w));
     } else {
-      DPB_CUDA(launch_k(bn_bwd_reduce_fold_kernel<false>, dim3(groups, (unsigned)slices), dim3(256), 0, S(stream), y, dout, scale, shift, save_mean, save_invstd, gamma, part_g, part_gx, opix, c, h, w, count, dgamma, dbeta, conv_dbias, coef, cnt));
+      DPB_CUDA(launch_k(bn_bwd_reduce_acc_kernel<false>, dim3(groups, (unsigned)slices), dim3(256), 0, S(stream), y, dout, scale, shift, save_mean, save_invstd, a, opix, c, h, w));
+      DPB_CUDA(launch_k(bn_bwd_apply_acc_kernel<false>, dim3(ablocks), dim3(256), 0, S(stream), y, dout, scale, shift, save_mean, save_invstd, gamma, a, t, count, dgamma, dbeta, conv_dbias, dy, units, c, h, w));
     }
-  } else {
+    return 0;
+  }
+  {
     const int pl = 256 / c4;
     int blocks = (int)((opix + pl - 1) / pl);
     if (blocks > kBnBwdBlocks) blocks = kBnBwdBlocks;
@@ -328,7 +303,6 @@ int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, 
     }
     DPB_CUDA(launch_k(bn_bwd_finalize_kernel, dim3((c + kFinCh - 1) / kFinCh), dim3(kFinCh, kFinRows), 0, S(stream), part_g, part_gx, blocks, c, count, gamma, save_mean, save_invstd, dgamma, dbeta, conv_dbias, coef));
   }
-  const long long units = opix * c4;
   const int ablocks = grid_for(units, 256, 148 * 16);
   if (pool) {
     DPB_CUDA(launch_k(bn_bwd_apply_kernel<true>, dim3(ablocks), dim3(256), 0, S(stream), y, dout, scale, shift, coef, dy, units, c, h, w));
@@ -964,9 +938,9 @@ int dpb_bn_relu_pool_bwd_noalloc(const float* y, const float* dout, const float*
   // cleared even though the array still holds the previous call's contents.
   float* part = scratch;
   float* coef = scratch + (size_t)2 * kBnBwdBlocks * kNoAllocMaxChannels;
-  // (no ticket counters: this variant keeps the separate reduce / finalize / apply launches)
-  return dpb_bn_relu_pool_bwd(y, dout, scale, shift, save_mean, save_invstd, gamma, part, coef, nullptr, dgamma, dbeta,
-                              conv_dbias, dy, n, h, w, c, pool, stream);
+  // (no accumulators: this variant keeps the separate reduce / finalize / apply launches and their scratch)
+  return dpb_bn_relu_pool_bwd(y, dout, scale, shift, save_mean, save_invstd, gamma, part, coef, nullptr, nullptr, dgamma,
+                              dbeta, conv_dbias, dy, n, h, w, c, pool, stream);
 }
 
 }  // extern "C"

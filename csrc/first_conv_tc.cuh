@@ -14,7 +14,7 @@
 // written once, in a fixed order: part_sum / part_sq are [gridDim.x][64].
 #pragma once
 #include "ptx.cuh"
-#include "bn_fold.cuh"
+#include "bn_acc.cuh"
 
 namespace dpb {
 
@@ -73,11 +73,12 @@ __device__ __forceinline__ void fc_tc_fetch_patch(const float* __restrict__ x, i
 }
 
 // x: [N][3][H][W] fp32 (NCHW).  w: [64][3][3][3] (KRSC).  y: [N*H*W][64].  part_sum / part_sq: [gridDim.x][64] or null.
-// bn.counters != null: the CTA that writes the last partial row also performs the BatchNorm finalize (bn_fold.cuh).
+// stat_acc (optional): [2][64] fixed-point BatchNorm accumulators (bn_acc.cuh) the CTA adds its column sums to.
 __global__ void __launch_bounds__(kFcTcThreads)
 first_conv_fprop_tc_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                            float* __restrict__ y, float* __restrict__ part_sum, float* __restrict__ part_sq, int N, int H,
-                           int W, const BnFoldArgs bn) {
+                           int W, unsigned long long* __restrict__ stat_acc) {
+  DPB_TRACE(8);
   pdl_prologue();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_align_1024(smem_raw);
@@ -121,6 +122,7 @@ first_conv_fprop_tc_kernel(const float* __restrict__ x, const float* __restrict_
   const int q = warp;                               // TMEM lane quarter
   uint32_t phase = 0;
   float acc_stat = 0.f;  // thread t: channel t & 63 of (t < 64 ? sum : sum of squares)
+  const bool want_stats = part_sum != nullptr || stat_acc != nullptr;
 
   float pre[kFcTcPrefetch];  // the next tile's patch, in flight during this tile's MMA and epilogue
   FcTcPatchPlan plan;
@@ -195,7 +197,7 @@ first_conv_fprop_tc_kernel(const float* __restrict__ x, const float* __restrict_
       s4.x += o.x; s4.y += o.y; s4.z += o.z; s4.w += o.w;
       t4.x += o.x * o.x; t4.y += o.y * o.y; t4.z += o.z * o.z; t4.w += o.w * o.w;
     }
-    if (part_sum != nullptr) {
+    if (want_stats) {
       s4.x += __shfl_xor_sync(0xffffffffu, s4.x, 16); s4.y += __shfl_xor_sync(0xffffffffu, s4.y, 16);
       s4.z += __shfl_xor_sync(0xffffffffu, s4.z, 16); s4.w += __shfl_xor_sync(0xffffffffu, s4.w, 16);
       t4.x += __shfl_xor_sync(0xffffffffu, t4.x, 16); t4.y += __shfl_xor_sync(0xffffffffu, t4.y, 16);
@@ -207,22 +209,15 @@ first_conv_fprop_tc_kernel(const float* __restrict__ x, const float* __restrict_
     }
     tc_fence_before();
     __syncthreads();  // TMEM and the A tile may be overwritten by the next tile; `red` is complete
-    if (part_sum != nullptr) {
+    if (want_stats) {
       const int which = tid >> 6, c = tid & 63;
 #pragma unroll
       for (int ww = 0; ww < 4; ++ww) acc_stat += red[(ww * 2 + which) * 64 + c];
     }
     tc_fence_after();
   }
-  if (part_sum != nullptr) {
-    (tid < 64 ? part_sum : part_sq)[(size_t)blockIdx.x * 64 + (tid & 63)] = acc_stat;
-    if (bn.counters != nullptr) {
-      volatile uint32_t* flag = slot + 1;
-      if (arrive_last(bn.counters, gridDim.x, tid, 0, kFcTcThreads, flag))
-        bn_finalize_cols(part_sum, part_sq, (int)gridDim.x, 64, 0, 64, bn, true, tid, 0, kFcTcThreads,
-                         reinterpret_cast<double*>(stg));
-    }
-  }
+  if (part_sum != nullptr) (tid < 64 ? part_sum : part_sq)[(size_t)blockIdx.x * 64 + (tid & 63)] = acc_stat;
+  if (stat_acc != nullptr) bn_acc_add(stat_acc + tid, acc_stat);  // tid < 64: sum of channel tid, else sum of squares
   __syncthreads();
   if (warp == 0) tmem_dealloc<64>(tmem);
 }

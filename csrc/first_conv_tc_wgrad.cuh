@@ -34,6 +34,7 @@ struct FcTcWgradSmem {
 __global__ void __launch_bounds__(kFcTcThreads, 1)
 first_conv_wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDy, const float* __restrict__ x,
                            float* __restrict__ partials, int N, int H, int W) {
+  DPB_TRACE(9);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_align_1024(smem_raw);
   uint8_t* sA = smem + FcTcWgradSmem::kA;

@@ -4,7 +4,7 @@
 // torch.optim.SGD's per-parameter add/mul_/add_ chain (reference main.py:36,103-104).  SURVEY.md §8 K9-K12.
 #pragma once
 #include "ptx.cuh"
-#include "bn_fold.cuh"
+#include "bn_acc.cuh"
 
 namespace dpb {
 
@@ -197,6 +197,7 @@ head_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const 
                 const long long* __restrict__ target, float* __restrict__ logits, float* __restrict__ dz,
                 float2* __restrict__ terms /* [B] (loss_i, hit_i) */, float* __restrict__ loss_out,
                 float* __restrict__ metrics, unsigned int* __restrict__ counter, int B, int K, int O) {
+  DPB_TRACE(10);
   pdl_prologue();
   extern __shared__ float4 s_w4[];  // [O][K/4]
   __shared__ float s_part[2][8];
@@ -280,6 +281,7 @@ __global__ void __launch_bounds__(256)
 head_bwd_kernel(const float* __restrict__ dz, const float* __restrict__ x, const float* __restrict__ w,
                 const float* __restrict__ grad_out, float* __restrict__ dx, float* __restrict__ dw,
                 float* __restrict__ db, int B, int K, int O, int nx, int nw) {
+  DPB_TRACE(11);
   pdl_prologue();
   __shared__ float s[8][kMaxClasses][33];
   const float g = grad_out ? grad_out[0] : 1.f;
@@ -353,6 +355,7 @@ head_bwd_kernel(const float* __restrict__ dz, const float* __restrict__ x, const
 __global__ void __launch_bounds__(256)
 sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, long long n4, float lr,
            float momentum, float wd, float grad_scale, int nesterov) {
+  DPB_TRACE(12);
   pdl_prologue();
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {

@@ -56,6 +56,39 @@ __device__ __forceinline__ void dev_fail(int code, int where, int aux0, int aux1
   __trap();
 }
 
+// ---------------------------------------------------------------- kernel timeline (experiments builds only)
+// With -DDPB_EXPERIMENTS every kernel stamps %globaltimer when thread 0 of block 0 enters and leaves it, into a buffer
+// registered with dpb_debug_set_trace(): [0] = number of records, then {kernel id, t_begin, t_end} triples.  That is how
+// tools/overlap_timeline.py shows a bucket's collective (side stream) running under the convolution kernels of earlier
+// layers inside one CUDA-graph replay.  Production builds compile all of it away.
+#ifdef DPB_EXPERIMENTS
+__device__ unsigned long long* g_dpb_trace = nullptr;
+constexpr int kTraceMaxRecords = 4096;
+struct TraceScope {
+  unsigned long long* rec;
+  __device__ __forceinline__ explicit TraceScope(int id) : rec(nullptr) {
+    if (threadIdx.x == 0 && threadIdx.y == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+      unsigned long long* t = g_dpb_trace;
+      if (t != nullptr) {
+        const unsigned long long slot = atomicAdd(t, 1ull);
+        if (slot < (unsigned long long)kTraceMaxRecords) {
+          rec = t + 1 + 3 * slot;
+          rec[0] = (unsigned long long)id;
+          rec[1] = globaltimer_ns();
+          rec[2] = 0;
+        }
+      }
+    }
+  }
+  __device__ __forceinline__ ~TraceScope() {
+    if (rec != nullptr) rec[2] = globaltimer_ns();
+  }
+};
+#define DPB_TRACE(id) ::dpb::TraceScope dpb_trace_scope_(id)
+#else
+#define DPB_TRACE(id) do { } while (0)
+#endif
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

@@ -1,8 +1,6 @@
 // Second phase of split-K for the tcgen05 convolution.  The conv CTAs leave fp32 partial tiles in the workspace
 // ([tile][split][128][NT]); this kernel sums them in split order (deterministic), adds the bias, stores the result with
-// 16-byte accesses and leaves one BatchNorm partial row (sum, sum of squares per channel) per row piece of a tile:
-// stat row index = m_tile * pieces + piece.  The block that writes the last row of a channel group also performs the
-// BatchNorm finalize (bn_fold.cuh) when the caller asked for it.
+// 16-byte accesses and adds the per-channel sum / sum of squares of its rows to the BatchNorm accumulators (bn_acc.cuh).
 //
 // This is the fallback split-K path: GEMMs whose split factor fits a thread-block cluster (<= 16) are reduced over
 // distributed shared memory inside conv_gemm_kernel and never come here.
@@ -24,10 +22,9 @@ __device__ __forceinline__ void f4_acc(float4& a, const float4& t) {
 template <int MODE>
 __global__ void __launch_bounds__(256)
 splitk_reduce_kernel(const ConvGemmParams p, int NT, int m_tiles, int n_tiles, int pieces) {
+  DPB_TRACE(4);
   pdl_prologue();
-  __shared__ __align__(16) unsigned char red_raw[256 * 64];  // [2][256] float4 column sums, later 2048 doubles for the finalize
-  __shared__ uint32_t last_flag;
-  float4 (*red)[256] = reinterpret_cast<float4 (*)[256]>(red_raw);
+  __shared__ float4 red[2][256];
   const int tile_id = blockIdx.x;
   const int m_tile = tile_id % m_tiles;
   const int n_tile = (tile_id / m_tiles) % n_tiles;
@@ -99,28 +96,24 @@ splitk_reduce_kernel(const ConvGemmParams p, int NT, int m_tiles, int n_tiles, i
     f4_acc(s0, acc);
     s1.x += acc.x * acc.x; s1.y += acc.y * acc.y; s1.z += acc.z * acc.z; s1.w += acc.w * acc.w;
   }
-  if (MODE == kFprop && p.stat_sum != nullptr) {
+  if (MODE == kFprop && p.stat_acc != nullptr) {
     red[0][threadIdx.x] = s0;
     red[1][threadIdx.x] = s1;
     __syncthreads();
-    if (threadIdx.x < 2 * C4) {
+    if (threadIdx.x < 2 * C4) {  // row lanes combined in lane order, then one fixed-point atomic per channel (bn_acc.cuh)
       const int which = threadIdx.x / C4, cc = threadIdx.x % C4;
       float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int l = 0; l < RL; ++l) f4_acc(a, red[which][l * C4 + cc]);
-      float* dst = which == 0 ? p.stat_sum : p.stat_sq;
-      *reinterpret_cast<float4*>(dst + (size_t)(m_tile * pieces + blockIdx.y) * p.N_total + n_tile * NT + cc * 4) = a;
-    }
-    // BatchNorm finalize by the block that delivers the last partial row of this channel group (bn_fold.cuh)
-    if (p.bn.counters != nullptr) {
-      if (arrive_last(p.bn.counters + n_tile, (unsigned)(m_tiles * pieces), (int)threadIdx.x, 0, 256, &last_flag))
-        bn_finalize_cols(p.stat_sum, p.stat_sq, p.stat_rows, p.N_total, n_tile * NT, NT, p.bn, n_tile == 0,
-                         (int)threadIdx.x, 0, 256, reinterpret_cast<double*>(red_raw));
+      unsigned long long* dst = p.stat_acc + (size_t)which * p.N_total + n_tile * NT + cc * 4;
+      bn_acc_add(dst + 0, a.x);
+      bn_acc_add(dst + 1, a.y);
+      bn_acc_add(dst + 2, a.z);
+      bn_acc_add(dst + 3, a.w);
     }
   }
 }
 
-// Row pieces per tile for the reduce grid: enough blocks to cover the GPU, at least 4, at most 128 / row-lanes, and
-// (fprop) no more BatchNorm partial rows than the caller allocated: 32 per tile up to 64 tiles, 4 per tile beyond.
+// Row pieces per tile for the reduce grid: enough blocks to cover the GPU, at least 4, at most 128 / row-lanes.
 inline int splitk_pieces(int tiles_total, int m_tiles, int nt) {
   const int max_by_lanes = 128 / (1024 / nt);  // NT 64 -> 8, 128 -> 16, 256 -> 32
   int cap = m_tiles <= 64 ? 32 : 4;

@@ -25,7 +25,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC", "-shared", "-cudart", "static",
 ]
 
-ABI_VERSION = 200  # must equal dpb_version() of the loaded library (bumped whenever the C ABI changes)
+ABI_VERSION = 202  # must equal dpb_version() of the loaded library (bumped whenever the C ABI changes)
 
 _lock = threading.Lock()
 _lib = None
@@ -59,9 +59,10 @@ def needs_build() -> bool:
     library), not by mtime: the tree may have been copied to another machine in any order."""
     if not os.path.exists(LIB_PATH) or not os.path.exists(HASH_PATH):
         return True
+    want = _source_hash() + ("+experiments" if os.environ.get("DPB_EXPERIMENTS") == "1" else "")
     try:
         with open(HASH_PATH) as fh:
-            return fh.read().strip() != _source_hash()
+            return fh.read().strip() != want
     except OSError:
         return True
 
@@ -117,15 +118,15 @@ _SIGNATURES = {
     "dpb_init_device": (c_int, []),
     "dpb_last_device_error": (c_int, [_I, POINTER(c_int)]),
     "dpb_debug_set_conv_dump": (c_int, [_P]),
+    "dpb_debug_set_trace": (c_int, [_P]),
     "dpb_conv_workspace_bytes": (c_size_t, []),
-    "dpb_conv_counter_bytes": (c_size_t, []),
-    "dpb_conv3x3_gemm": (c_int, [_I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, POINTER(c_int), _P]),
-    "dpb_conv3x3_fprop_bn": (c_int, [_I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _F, _F, _P, _I, _I, _P]),
-    "dpb_first_conv_fprop_bn": (c_int, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _P, _P, _P, _P, _F, _F, _P, _P]),
+    "dpb_conv3x3_gemm": (c_int, [_I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "dpb_first_conv_uses_tensor_cores": (c_int, [_I, _I]),
+    "dpb_bn_relu_pool_fwd_train": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _F, _F, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dpb_conv_last_launches": (c_int, []),
     "dpb_set_tuning": (c_int, [_I, _I]),
     "dpb_first_conv_blocks": (c_int, [_I, _I, _I]),
-    "dpb_first_conv_fprop": (c_int, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "dpb_first_conv_fprop": (c_int, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "dpb_first_conv_wgrad_blocks": (c_int, []),
     "dpb_first_conv_wgrad": (c_int, [_P, _P, _P, _P, _I, _I, _I, _P]),
     "dpb_bn_finalize": (c_int, [_P, _P, _I, _I, c_double, _P, _P, _P, _P, _P, _F, _F, _P, _P, _P, _P, _P]),
@@ -133,7 +134,7 @@ _SIGNATURES = {
     "dpb_bn_relu_pool_fwd": (c_int, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dpb_bn_bwd_blocks": (c_int, []),
     "dpb_bn_bwd_launches": (c_int, [_I, _I]),
-    "dpb_bn_relu_pool_bwd": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dpb_bn_relu_pool_bwd": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dpb_relu_fwd": (c_int, [_P, _P, _LL, _P]),
     "dpb_relu_bwd": (c_int, [_P, _P, _P, _LL, _P]),
     "dpb_maxpool2x2_fwd": (c_int, [_P, _P, _I, _I, _I, _I, _P]),
@@ -194,7 +195,7 @@ _SIGNATURES = {
 
 # dpb_set_tuning keys and the environment variables that set them at load time (include/dpb200.h)
 TUNING_ENV = ((0, "DPB_CONV_TARGET_CTAS"), (1, "DPB_CONV_NT"), (2, "DPB_COMM_BLOCKS"), (3, "DPB_CONV_MIN_K_ITERS"),
-              (4, "DPB_PDL"), (5, "DPB_CONV_CLUSTER_MAX"), (7, "DPB_FIRST_TC"), (8, "DPB_BN_FOLD"), (11, "DPB_COMM_WEAK"),
+              (4, "DPB_PDL"), (5, "DPB_CONV_CLUSTER_MAX"), (7, "DPB_FIRST_TC"), (11, "DPB_COMM_WEAK"),
               (13, "DPB_DDP_BLOCKS"), (14, "DPB_NVLS"), (15, "DPB_NVLS_BLOCKS"))
 
 

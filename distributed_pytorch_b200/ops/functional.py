@@ -63,20 +63,28 @@ class _ConvBnReluPool(torch.autograd.Function):
             xin = _as_nhwc(x.detach())
         y = K.nhwc_empty(n, cout, h, w, x.device)
         if training:
-            # conv + batch statistics; the finalize (scale/shift, running stats) is folded into the producing kernel
-            if first:
-                stats = K.first_conv_fprop_bn(xin, wk, conv_b, y, bn_w, bn_b, running_mean, running_var, nbt, momentum,
-                                              eps)
+            # conv kernels add the per-channel sums to fixed-point accumulators; the BatchNorm kernel derives scale and
+            # shift from them in its prologue (no partial rows, no finalize launch) and clears them again
+            if first and not K.first_conv_on_tensor_cores(h, w):
+                ps, pq, parts = K.first_conv_fprop(xin, wk, conv_b, y, True)
+                stats = K.bn_finalize(ps, pq, parts, cout, float(n * h * w), bn_w, bn_b, running_mean, running_var, nbt,
+                                      momentum, eps)
+                out = K.bn_relu_pool_fwd(y, stats[0], stats[1], pool)
             else:
-                stats = K.conv3x3_fprop_bn(n, h, w, cin, cout, xin, wk, y, conv_b, bn_w, bn_b, running_mean,
-                                           running_var, nbt, momentum, eps)
+                acc, ticket = K.scratch(x.device).next_acc()
+                if first:
+                    K.first_conv_fprop(xin, wk, conv_b, y, False, stat_acc=acc)
+                else:
+                    K.conv3x3_gemm(0, n, h, w, cin, cout, xin, None, wk, y, conv_b, stat_acc=acc)
+                out, stats = K.bn_relu_pool_fwd_train(y, acc, ticket, bn_w, bn_b, running_mean, running_var, nbt,
+                                                      momentum, eps, pool)
         else:
             if first:
                 K.first_conv_fprop(xin, wk, conv_b, y, False)
             else:
-                K.conv3x3_gemm(0, n, h, w, cin, cout, xin, None, wk, y, conv_b, want_stats=False)
+                K.conv3x3_gemm(0, n, h, w, cin, cout, xin, None, wk, y, conv_b)
             stats = K.bn_eval_scale_shift(cout, bn_w, bn_b, running_mean, running_var, eps)
-        out = K.bn_relu_pool_fwd(y, stats[0], stats[1], pool)
+            out = K.bn_relu_pool_fwd(y, stats[0], stats[1], pool)
         ctx.pool = pool
         ctx.first = first
         ctx.training = training
@@ -107,17 +115,20 @@ class _ConvBnReluPool(torch.autograd.Function):
             # the weight gradient feeds nothing further down the chain: run it next to the data gradient (and the
             # previous block's BatchNorm backward) on the device's second stream.  Only when autograd will adopt the
             # result without launching an accumulation kernel on this stream (param.grad is None).
-            if K.wgrad_overlap() and conv_w.grad is None and ctx.needs_input_grad[0]:
+            side_by_side = K.wgrad_overlap() and conv_w.grad is None and ctx.needs_input_grad[0]
+            if side_by_side:
                 lane = K.wgrad_lane(y.device)
                 lane.fork()
                 with torch.cuda.stream(lane.stream):
-                    K.conv3x3_gemm(2, n, h, w, cin, cout, dy, xin, wk, d_conv_w, side=True)
+                    K.conv3x3_gemm(2, n, h, w, cin, cout, dy, xin, wk, d_conv_w, side=True,
+                                   target_ctas=K.BWD_TARGET_CTAS)
                 lane.hold(dy, xin)  # not d_conv_w: AccumulateGrad only adopts a gradient nobody else references
             else:
                 K.conv3x3_gemm(2, n, h, w, cin, cout, dy, xin, wk, d_conv_w)
             if ctx.needs_input_grad[0]:
                 dx = K.nhwc_empty(n, cin, h, w, y.device)
-                K.conv3x3_gemm(1, n, h, w, cin, cout, dy, None, wk, dx)
+                K.conv3x3_gemm(1, n, h, w, cin, cout, dy, None, wk, dx,
+                               target_ctas=K.BWD_TARGET_CTAS if side_by_side else 0)
         return dx, d_conv_w, d_conv_b, d_bn_w, d_bn_b, None, None, None, None, None, None, None
 
 
@@ -157,7 +168,7 @@ class _Conv3x3(torch.autograd.Function):
             K.first_conv_fprop(xin, wk, conv_b, y, False)
         else:
             xin = _as_nhwc(x.detach())
-            K.conv3x3_gemm(0, n, h, w, cin, cout, xin, None, wk, y, conv_b, want_stats=False)
+            K.conv3x3_gemm(0, n, h, w, cin, cout, xin, None, wk, y, conv_b)
         ctx.first = first
         ctx.params = (conv_w, conv_b)
         ctx.save_for_backward(xin, wk)

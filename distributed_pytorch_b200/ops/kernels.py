@@ -15,8 +15,8 @@ import torch
 from .. import _native as N
 
 __all__ = [
-    "Scratch", "scratch", "conv3x3_gemm", "conv3x3_fprop_bn", "first_conv_fprop", "first_conv_fprop_bn",
-    "first_conv_wgrad", "bn_finalize", "bn_eval_scale_shift", "bn_relu_pool_fwd", "bn_relu_pool_bwd", "linear_fwd",
+    "Scratch", "scratch", "conv3x3_gemm", "first_conv_fprop", "first_conv_wgrad", "bn_finalize",
+    "bn_eval_scale_shift", "bn_relu_pool_fwd", "bn_relu_pool_fwd_train", "bn_relu_pool_bwd", "linear_fwd",
     "linear_bwd", "cross_entropy_fwd", "cross_entropy_bwd", "head_supported", "head_fwd", "head_bwd", "augment_batch",
     "sgd_step", "is_nhwc", "nhwc_empty",
 ]
@@ -35,8 +35,8 @@ def nhwc_empty(n: int, c: int, h: int, w: int, device) -> torch.Tensor:
 
 
 class Scratch:
-    """Per-device scratch the kernels share (stream-ordered reuse): split-K partial tiles of the workspace path,
-    self-resetting ticket counters of the folded finalize steps, BatchNorm-backward partial sums and coefficients,
+    """Per-device scratch the kernels share (stream-ordered reuse): split-K partial tiles of the workspace path, the ring
+    of BatchNorm accumulator slots, BatchNorm-backward partial rows and coefficients of the three-launch path,
     first-layer wgrad partials."""
 
     def __init__(self, device: torch.device):
@@ -44,8 +44,13 @@ class Scratch:
         N.init_device(device.index)
         self.device = device
         self.conv_ws = torch.empty(lib.dpb_conv_workspace_bytes() // 4, device=device, dtype=torch.float32)
-        self.conv_counters = torch.zeros(lib.dpb_conv_counter_bytes() // 4, device=device, dtype=torch.int32)
-        self.bn_counters = torch.zeros(64, device=device, dtype=torch.int32)
+        # BatchNorm accumulators (bn_acc.cuh): a ring of zeroed [2][1024] int64 slots + one ticket each.  A producer
+        # (conv / backward reduce) fills a slot, its consumer clears it again, so a slot is clean whenever its turn
+        # comes round; 64 slots cover every BatchNorm of a forward + backward pass of the deepest VGG twice over.
+        self.acc_slots = 64
+        self.bn_acc = torch.zeros((self.acc_slots, 2 * 1024), device=device, dtype=torch.int64)
+        self.bn_tickets = torch.zeros(self.acc_slots, device=device, dtype=torch.int32)
+        self._acc_next = 0
         self.head_counter = torch.zeros(4, device=device, dtype=torch.int32)
         # second split-K workspace: weight-gradient GEMMs running on the side stream (WgradLane) must not share partial
         # tiles with the data-gradient GEMM that runs next to them
@@ -54,6 +59,12 @@ class Scratch:
         self.bn_part = torch.empty(2 * self.bn_blocks * 1024, device=device, dtype=torch.float32)
         self.bn_coef = torch.empty(3 * 1024, device=device, dtype=torch.float32)
         self.fc_wgrad_part = torch.empty(lib.dpb_first_conv_wgrad_blocks() * 64 * 27, device=device, dtype=torch.float32)
+
+    def next_acc(self):
+        """(accumulator slot, its ticket) for one producer -> consumer pair of launches."""
+        i = self._acc_next
+        self._acc_next = (i + 1) % self.acc_slots
+        return self.bn_acc[i], self.bn_tickets[i:i + 1]
 
 
 _scratch: dict[int, Scratch] = {}
@@ -116,13 +127,17 @@ class WgradLane:
 
 
 _lanes: dict[int, WgradLane] = {}
-_wgrad_overlap = os.environ.get("DPB_WGRAD_OVERLAP", "0") == "1"
+_wgrad_overlap = os.environ.get("DPB_WGRAD_OVERLAP", "1") == "1"
+# CTA count each of the two concurrent GEMMs (data gradient on the main stream, weight gradient on the lane) aims for:
+# one per SM, so that together they fill the two CTA slots of every SM.
+BWD_TARGET_CTAS = int(os.environ.get("DPB_BWD_TARGET_CTAS", "148"))
 
 
 def set_wgrad_overlap(enabled: bool) -> None:
-    """Weight-gradient kernels on a second stream (``DPB_WGRAD_OVERLAP=1``).  Off by default: measured on B200 it is
-    neutral at batch 256 (1.0741 vs 1.0736 ms/step) and +1.3 % at batch 32 -- both conv CTA slots of every SM are
-    already taken by the data-gradient GEMM, so the second stream only fills wave tails."""
+    """Weight-gradient kernels on a second stream next to the data-gradient GEMM (default on; ``DPB_WGRAD_OVERLAP=0``
+    switches it off).  Round 1 measured this as neutral because each GEMM was split to fill both CTA slots of every SM
+    on its own; with each of the two asking for one CTA per SM (``BWD_TARGET_CTAS``) they genuinely run side by side:
+    0.952 -> 0.900 ms/step at batch 256, 0.483 -> 0.455 ms at batch 32 (profiles/step_variants.md)."""
     global _wgrad_overlap
     _wgrad_overlap = bool(enabled)
 
@@ -149,53 +164,32 @@ def active_wgrad_lane(device: torch.device) -> Optional[WgradLane]:
 
 def conv3x3_gemm(mode: int, n: int, h: int, w: int, cin: int, cout: int, inp: torch.Tensor,
                  inp2: Optional[torch.Tensor], weight: torch.Tensor, out: torch.Tensor,
-                 bias: Optional[torch.Tensor] = None, want_stats: bool = False, nt: int = 0, splits: int = 0,
-                 side: bool = False):
-    """tcgen05 implicit-GEMM conv. mode 0 fprop / 1 dgrad / 2 wgrad. Returns (stat_sum, stat_sq, m_tiles) for fprop
-    with ``want_stats`` else None.  ``side`` selects the second split-K workspace (see :class:`WgradLane`)."""
+                 bias: Optional[torch.Tensor] = None, stat_acc: Optional[torch.Tensor] = None, nt: int = 0,
+                 splits: int = 0, side: bool = False, target_ctas: int = 0) -> None:
+    """tcgen05 implicit-GEMM conv. mode 0 fprop / 1 dgrad / 2 wgrad.  ``stat_acc`` (fprop): zeroed int64 [2*cout]
+    accumulators that receive the BatchNorm batch statistics (fixed point, 2^-20).  ``side`` selects the second split-K
+    workspace (see :class:`WgradLane`)."""
     lib = N.require()
     sc = scratch(out.device)
     conv_ws = sc.conv_ws_side if side else sc.conv_ws
-    stat_sum = stat_sq = None
-    m_tiles = ctypes.c_int(0)
-    if want_stats:
-        stat_sum, stat_sq = _stat_buffers(n, h, w, cout, out.device)
     N.check(lib.dpb_conv3x3_gemm(mode, n, h, w, cin, cout, N.ptr(inp), N.ptr(inp2), N.ptr(weight), N.ptr(out),
-                                 N.ptr(bias), N.ptr(stat_sum), N.ptr(stat_sq), N.ptr(conv_ws), nt, splits,
-                                 ctypes.byref(m_tiles), N.stream()),
+                                 N.ptr(bias), N.ptr(stat_acc), N.ptr(conv_ws), nt, splits, target_ctas, N.stream()),
             "dpb_conv3x3_gemm")
     N.count_launches(lib.dpb_conv_last_launches())
-    if want_stats:
-        return stat_sum, stat_sq, m_tiles.value
-    return None
 
 
-def _stat_buffers(n: int, h: int, w: int, cout: int, device):
-    tiles = (n * h * w + 127) // 128
-    tiles *= 32 if tiles <= 64 else 4  # split-K leaves up to 32 (<= 64 tiles) / 4 partial rows per tile, else 1
-    return (torch.empty((tiles, cout), device=device, dtype=torch.float32),
-            torch.empty((tiles, cout), device=device, dtype=torch.float32))
+ACC_SCALE_FWD = float(1 << 20)
 
 
-def conv3x3_fprop_bn(n: int, h: int, w: int, cin: int, cout: int, x: torch.Tensor, weight: torch.Tensor,
-                     y: torch.Tensor, bias, gamma, beta, running_mean, running_var, nbt, momentum: float, eps: float,
-                     nt: int = 0, splits: int = 0) -> torch.Tensor:
-    """Conv fprop + training-mode BatchNorm statistics; returns stats = (4, C): scale, shift, mean, invstd.  The
-    finalize runs inside the conv (or split-K reduce) kernel whenever the partial rows are few enough."""
-    lib = N.require()
-    sc = scratch(y.device)
-    stat_sum, stat_sq = _stat_buffers(n, h, w, cout, y.device)
-    stats = torch.empty((4, cout), device=y.device, dtype=torch.float32)
-    N.check(lib.dpb_conv3x3_fprop_bn(n, h, w, cin, cout, N.ptr(x), N.ptr(weight), N.ptr(y), N.ptr(bias),
-                                     N.ptr(stat_sum), N.ptr(stat_sq), N.ptr(sc.conv_ws), N.ptr(sc.conv_counters),
-                                     N.ptr(gamma), N.ptr(beta), N.ptr(running_mean), N.ptr(running_var), N.ptr(nbt),
-                                     momentum, eps, N.ptr(stats), nt, splits, N.stream()), "dpb_conv3x3_fprop_bn")
-    N.count_launches(lib.dpb_conv_last_launches())
-    return stats
+def acc_to_float(acc: torch.Tensor, c: int):
+    """(sum, sum of squares) per channel out of a forward accumulator slot (tests)."""
+    return acc[:c].double() / ACC_SCALE_FWD, acc[c:2 * c].double() / ACC_SCALE_FWD
 
 
 def first_conv_fprop(x_nchw: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], y: torch.Tensor,
-                     want_stats: bool):
+                     want_stats: bool, stat_acc: Optional[torch.Tensor] = None):
+    """First layer.  Statistics as partial rows (``want_stats``: returns (part_sum, part_sq, rows) for bn_finalize) or
+    into ``stat_acc`` (tensor-core kernel only)."""
     lib = N.require()
     n, _, h, w = x_nchw.shape
     blocks = lib.dpb_first_conv_blocks(n, h, w)
@@ -203,28 +197,14 @@ def first_conv_fprop(x_nchw: torch.Tensor, weight: torch.Tensor, bias: Optional[
     if want_stats:
         ps = torch.empty((blocks, 64), device=y.device, dtype=torch.float32)
         pq = torch.empty((blocks, 64), device=y.device, dtype=torch.float32)
-    N.check(lib.dpb_first_conv_fprop(N.ptr(x_nchw), N.ptr(weight), N.ptr(bias), N.ptr(y), N.ptr(ps), N.ptr(pq), n, h,
-                                     w, N.stream()), "dpb_first_conv_fprop")
+    N.check(lib.dpb_first_conv_fprop(N.ptr(x_nchw), N.ptr(weight), N.ptr(bias), N.ptr(y), N.ptr(ps), N.ptr(pq),
+                                     N.ptr(stat_acc), n, h, w, N.stream()), "dpb_first_conv_fprop")
     N.count_launches(1)
     return ps, pq, blocks
 
 
-def first_conv_fprop_bn(x_nchw: torch.Tensor, weight: torch.Tensor, bias, y: torch.Tensor, gamma, beta, running_mean,
-                        running_var, nbt, momentum: float, eps: float) -> torch.Tensor:
-    """First layer + BatchNorm statistics (finalize folded into the kernel's last block); returns stats (4, 64)."""
-    lib = N.require()
-    n, _, h, w = x_nchw.shape
-    sc = scratch(y.device)
-    blocks = lib.dpb_first_conv_blocks(n, h, w)
-    ps = torch.empty((blocks, 64), device=y.device, dtype=torch.float32)
-    pq = torch.empty((blocks, 64), device=y.device, dtype=torch.float32)
-    stats = torch.empty((4, 64), device=y.device, dtype=torch.float32)
-    N.check(lib.dpb_first_conv_fprop_bn(N.ptr(x_nchw), N.ptr(weight), N.ptr(bias), N.ptr(y), N.ptr(ps), N.ptr(pq), n, h,
-                                        w, N.ptr(sc.conv_counters), N.ptr(gamma), N.ptr(beta), N.ptr(running_mean),
-                                        N.ptr(running_var), N.ptr(nbt), momentum, eps, N.ptr(stats), N.stream()),
-            "dpb_first_conv_fprop_bn")
-    N.count_launches(lib.dpb_conv_last_launches())
-    return stats
+def first_conv_on_tensor_cores(h: int, w: int) -> bool:
+    return bool(N.require().dpb_first_conv_uses_tensor_cores(h, w))
 
 
 def first_conv_wgrad(x_nchw: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor):
@@ -267,18 +247,38 @@ def bn_relu_pool_fwd(y: torch.Tensor, scale, shift, pool: bool) -> torch.Tensor:
     return out
 
 
-def bn_relu_pool_bwd(y, dout, stats, gamma, dgamma, dbeta, conv_dbias, pool: bool) -> torch.Tensor:
-    """stats = (4, C) tensor from bn_finalize. Writes dgamma/dbeta, returns dY (NHWC, conv resolution)."""
+def bn_relu_pool_fwd_train(y: torch.Tensor, acc: torch.Tensor, ticket: torch.Tensor, gamma, beta, running_mean,
+                           running_var, nbt, momentum: float, eps: float, pool: bool):
+    """Training-mode BatchNorm + ReLU (+ pool) straight from the accumulators the conv filled.  Returns (out, stats)
+    with stats = (4, C): scale, shift, mean, invstd."""
+    lib = N.require()
+    n, c, h, w = y.shape
+    out = nhwc_empty(n, c, h // 2 if pool else h, w // 2 if pool else w, y.device)
+    stats = torch.empty((4, c), device=y.device, dtype=torch.float32)
+    N.check(lib.dpb_bn_relu_pool_fwd_train(N.ptr(y), N.ptr(acc), N.ptr(ticket), N.ptr(gamma), N.ptr(beta),
+                                           N.ptr(running_mean), N.ptr(running_var), N.ptr(nbt), momentum, eps,
+                                           N.ptr(stats), N.ptr(out), n, h, w, c, int(pool), N.stream()),
+            "dpb_bn_relu_pool_fwd_train")
+    N.count_launches(1)
+    return out, stats
+
+
+def bn_relu_pool_bwd(y, dout, stats, gamma, dgamma, dbeta, conv_dbias, pool: bool, use_acc: bool = True) -> torch.Tensor:
+    """stats = (4, C): scale, shift, mean, invstd. Writes dgamma/dbeta, returns dY (NHWC, conv resolution).
+    ``use_acc``: two launches through the fixed-point accumulators; else reduce / finalize / apply with scratch rows."""
     lib = N.require()
     n, c, h, w = y.shape
     sc = scratch(y.device)
     dy = torch.empty_like(y)
+    acc = ticket = None
+    if use_acc and c % 32 == 0:
+        acc, ticket = sc.next_acc()
     N.check(lib.dpb_bn_relu_pool_bwd(N.ptr(y), N.ptr(dout), N.ptr(stats[0]), N.ptr(stats[1]), N.ptr(stats[2]),
                                      N.ptr(stats[3]), N.ptr(gamma), N.ptr(sc.bn_part), N.ptr(sc.bn_coef),
-                                     N.ptr(sc.bn_counters), N.ptr(dgamma), N.ptr(dbeta), N.ptr(conv_dbias), N.ptr(dy),
-                                     n, h, w, c, int(pool), N.stream()),
+                                     N.ptr(acc), N.ptr(ticket), N.ptr(dgamma), N.ptr(dbeta), N.ptr(conv_dbias),
+                                     N.ptr(dy), n, h, w, c, int(pool), N.stream()),
             "dpb_bn_relu_pool_bwd")
-    N.count_launches(lib.dpb_bn_bwd_launches(c, 1))
+    N.count_launches(lib.dpb_bn_bwd_launches(c, int(acc is not None)))
     return dy
 
 

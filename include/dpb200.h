@@ -33,40 +33,33 @@ int dpb_init_device(void);
 int dpb_last_device_error(int device, int* out6);
 /* Bring-up aid, only in builds with -DDPB_EXPERIMENTS (tools/conv_timing.py): per-CTA trace of the conv kernel. */
 int dpb_debug_set_conv_dump(void* buf);
-/* Scratch needed by the tensor-core convolution: split-K partial tiles of the workspace path, and the ticket counters
- * (zero-initialised by the caller, self-resetting) of the folded BatchNorm finalize. */
+/* Experiments builds: every kernel records {id, globaltimer at entry, at exit} of its block 0 into buf
+ * (uint64: [0] = record count, then triples; room for 4096 records).  NULL switches it off.  tools/overlap_timeline.py */
+int dpb_debug_set_trace(void* buf);
+/* Scratch needed by the tensor-core convolution: split-K partial tiles of the workspace path. */
 size_t dpb_conv_workspace_bytes(void);
-size_t dpb_conv_counter_bytes(void);
 
 /* ---- convolution (ref: model.py:18-23 -> aten convolution / convolution_backward) ------------------------------ */
-/* mode 0 fprop: in = X, w = W, out = Y (+bias, + BatchNorm partial sums if stat_sum != NULL)
+/* mode 0 fprop: in = X, w = W, out = Y (+bias)
  * mode 1 dgrad: in = dY, w = W, out = dX
  * mode 2 wgrad: in = dY, in2 = X, out = dW
- * nt / splits: 0 = heuristic.  Split-K factors that are powers of two up to 16 are reduced inside the kernel by a
+ * nt / splits / target_ctas: 0 = heuristic (target_ctas: CTA count the split-K heuristic aims for in this call, e.g.
+ * one per SM for two GEMMs that share the GPU on two streams).  Split-K factors that are powers of two up to 16 are reduced inside the kernel by a
  * thread-block cluster over distributed shared memory; other factors go through `workspace` and a reduce kernel.
- * stat_rows_out (optional) receives the number of rows written to stat_sum / stat_sq (at most 32 per 128-pixel tile
- * up to 64 tiles, 4 per tile beyond). */
+ * stat_acc (fprop, optional): BatchNorm batch statistics -- [2][cout] 64-bit fixed-point accumulators (2^-20 units; zero
+ * on entry) to which the kernels add the per-channel sum and sum of squares of Y; dpb_bn_relu_pool_fwd_train consumes
+ * and clears them.  Integer atomics make the totals independent of the arrival order. */
 int dpb_conv3x3_gemm(int mode, int n, int h, int w, int cin, int cout, const float* in, const float* in2,
-                     const float* weight, float* out, const float* bias, float* stat_sum, float* stat_sq,
-                     void* workspace, int nt, int splits, int* stat_rows_out, dpb_stream_t stream);
-/* fprop + training-mode BatchNorm statistics: y = conv(x) + bias, then stats4 = [scale | shift | mean | invstd] ([4][cout])
- * and the running statistics / num_batches_tracked update.  The finalize runs inside the conv (or reduce) kernel, in
- * the block that delivers the last partial row; `counters` = dpb_conv_counter_bytes() of zeroed device memory.
- * (ref: model.py:18-24) */
-int dpb_conv3x3_fprop_bn(int n, int h, int w, int cin, int cout, const float* x, const float* weight, float* y,
-                         const float* bias, float* stat_sum, float* stat_sq, void* workspace, void* counters,
-                         const float* gamma, const float* beta, float* running_mean, float* running_var,
-                         long long* num_batches_tracked, float momentum, float eps, float* stats4, int nt, int splits,
-                         dpb_stream_t stream);
+                     const float* weight, float* out, const float* bias, void* stat_acc, void* workspace, int nt,
+                     int splits, int target_ctas, dpb_stream_t stream);
 /* Heuristic knobs (the Python loader also reads them from the environment variable in brackets).
  *  0 [DPB_CONV_TARGET_CTAS]  CTA count the split-K heuristic aims for (default 296 = two per SM)
  *  1 [DPB_CONV_NT]           preferred N tile (64 / 128 / 256, default 128) when it divides the GEMM N extent
  *  2 [DPB_COMM_BLOCKS]       default grid cap of the collective kernels (default 64, at most 128)
  *  3 [DPB_CONV_MIN_K_ITERS]  K iterations (of 32) a split must keep (default 8)
  *  4 [DPB_PDL]               programmatic dependent launch on every compute kernel (default 0)
- *  5 [DPB_CONV_CLUSTER_MAX]  largest split-K factor reduced over distributed shared memory (1 = never, default 16)
+ *  5 [DPB_CONV_CLUSTER_MAX]  largest split-K factor reduced over distributed shared memory (1 = never, default 8)
  *  7 [DPB_FIRST_TC]          first (Cin = 3) layer on the tensor cores when the image tiles into 128 pixels (default 1)
- *  8 [DPB_BN_FOLD]           BatchNorm finalize steps folded into their producers' last block (default 1)
  * 11 [DPB_COMM_WEAK]         two-shot all-reduce payload with weak accesses (default 0)
  * 12 [DPB_PEER_TIMEOUT_MS]   wall-clock budget of a peer-signal wait (default 120000)
  * 13 [DPB_DDP_BLOCKS]        grid of a per-bucket collective launched next to backward (default 24)
@@ -74,18 +67,15 @@ int dpb_conv3x3_fprop_bn(int n, int h, int w, int cin, int cout, const float* x,
  * 15 [DPB_NVLS_BLOCKS]       its grid (default 32)
  * Returns non-zero for an unknown key / bad value. */
 int dpb_set_tuning(int key, int value);
-/* Kernels launched by the calling thread's most recent dpb_conv3x3_gemm / dpb_conv3x3_fprop_bn /
- * dpb_first_conv_fprop_bn (1, 2 when split-K adds its reduce or the finalize is a launch of its own, ...). */
+/* Kernels launched by the calling thread's most recent dpb_conv3x3_gemm (1, or 2 when split-K adds its reduce). */
 int dpb_conv_last_launches(void);
-/* First layer (Cin = 3, Cout = 64): x is NCHW.  part_* : [dpb_first_conv_blocks(n,h,w)][64]. */
+/* First layer (Cin = 3, Cout = 64): x is NCHW.  Statistics either as partial rows part_* :
+ * [dpb_first_conv_blocks(n,h,w)][64] (for dpb_bn_finalize) or into stat_acc as above (tensor-core kernel only:
+ * dpb_first_conv_uses_tensor_cores); any of them may be NULL. */
 int dpb_first_conv_blocks(int n, int h, int w);
+int dpb_first_conv_uses_tensor_cores(int h, int w);
 int dpb_first_conv_fprop(const float* x_nchw, const float* weight, const float* bias, float* y, float* part_sum,
-                         float* part_sq, int n, int h, int w, dpb_stream_t stream);
-/* ... with the BatchNorm finalize folded in (see dpb_conv3x3_fprop_bn). */
-int dpb_first_conv_fprop_bn(const float* x_nchw, const float* weight, const float* bias, float* y, float* part_sum,
-                            float* part_sq, int n, int h, int w, void* counters, const float* gamma, const float* beta,
-                            float* running_mean, float* running_var, long long* num_batches_tracked, float momentum,
-                            float eps, float* stats4, dpb_stream_t stream);
+                         float* part_sq, void* stat_acc, int n, int h, int w, dpb_stream_t stream);
 /* partials: [dpb_first_conv_wgrad_blocks()][1728] scratch; dw: [64][3][3][3]. */
 int dpb_first_conv_wgrad_blocks(void);
 int dpb_first_conv_wgrad(const float* x_nchw, const float* dy, float* partials, float* dw, int n, int h, int w,
@@ -100,18 +90,27 @@ int dpb_bn_eval_scale_shift(int c, const float* gamma, const float* beta, const 
                             const float* running_var, float eps, float* scale, float* shift, dpb_stream_t stream);
 int dpb_bn_relu_pool_fwd(const float* y, const float* scale, const float* shift, float* out, int n, int h, int w,
                          int c, int pool, dpb_stream_t stream);
-/* Backward of the fused block.  part: scratch [2][dpb_bn_bwd_blocks()][c]; coef: scratch [3][c].
- * counters: 32 zeroed uint32 (self-resetting) -- with them (and c a multiple of 32) the reduction and the finalize are
- * ONE launch (the block that delivers a channel group's last partial row finishes the group), then the apply pass;
- * NULL keeps the three separate launches.
+/* Training-mode forward straight from the accumulators the conv filled: every block derives scale / shift in its
+ * prologue, block 0 publishes stats4 = [scale | shift | mean | invstd] ([4][c], needed by the backward pass) and updates
+ * the running statistics / num_batches_tracked; the last block clears `acc`.  ticket: one zeroed uint32, self-resetting.
+ * No finalize launch.  (ref: model.py:24-25,16) */
+int dpb_bn_relu_pool_fwd_train(const float* y, void* acc, void* ticket, const float* gamma, const float* beta,
+                               float* running_mean, float* running_var, long long* num_batches_tracked, float momentum,
+                               float eps, float* stats4, float* out, int n, int h, int w, int c, int pool,
+                               dpb_stream_t stream);
+/* Backward of the fused block.
+ * With acc ([2][c] zeroed 64-bit accumulators, cleared again by the call) and ticket (one zeroed uint32) and c a
+ * multiple of 32: TWO launches -- column sums of g and g*xhat into the accumulators, then the apply pass, which derives
+ * its coefficients from them.  part / coef are not used then.
+ * With acc == NULL: three launches (reduce into part: scratch [2][dpb_bn_bwd_blocks()][c], finalize into coef: scratch
+ * [3][c], apply).
  * conv_dbias (optional): gradient of the preceding conv's bias, exactly zero under training-mode BatchNorm. */
 int dpb_bn_bwd_blocks(void);
-/* Kernels dpb_bn_relu_pool_bwd launches: 2 with counters and c % 32 == 0, else 3. */
-int dpb_bn_bwd_launches(int c, int with_counters);
+int dpb_bn_bwd_launches(int c, int with_acc);
 int dpb_bn_relu_pool_bwd(const float* y, const float* dout, const float* scale, const float* shift,
                          const float* save_mean, const float* save_invstd, const float* gamma, float* part,
-                         float* coef, void* counters, float* dgamma, float* dbeta, float* conv_dbias, float* dy, int n,
-                         int h, int w, int c, int pool, dpb_stream_t stream);
+                         float* coef, void* acc, void* ticket, float* dgamma, float* dbeta, float* conv_dbias, float* dy,
+                         int n, int h, int w, int c, int pool, dpb_stream_t stream);
 
 /* ---- The same layer types on their own (ref: model.py:16-25, any arrangement other than conv->bn->relu[->pool]) ---- */
 int dpb_relu_fwd(const float* x, float* y, long long n, dpb_stream_t stream);

@@ -88,10 +88,16 @@ def test_training_trajectory_and_graph_step():
         assert torch.allclose(p, q, rtol=1e-5, atol=1e-6), k
 
 
-def test_wgrad_second_stream_is_bit_identical():
-    """Weight gradients on the second compute stream (K.WgradLane): same kernels, so eager and captured steps must
-    reproduce the single-stream run bit for bit, and gradients must still land in the arena in place."""
+@pytest.mark.parametrize("same_splits", [True, False])
+def test_wgrad_second_stream_is_bit_identical(same_splits):
+    """Weight gradients on the second compute stream (K.WgradLane).  With the same split-K factors as the single-stream
+    run (same_splits) it is the same arithmetic, so eager and captured steps must reproduce that run bit for bit; with
+    the shipped setting (each of the two concurrent GEMMs asks for one CTA per SM, so the split factors differ) the
+    trajectories must agree to rounding.  Gradients must land in the arena in place either way."""
     from distributed_pytorch_b200.ops import kernels as K
+    saved_target, saved_overlap = K.BWD_TARGET_CTAS, K.wgrad_overlap()
+    if same_splits:
+        K.BWD_TARGET_CTAS = 0
     _, base = _pair(5)
     lane = copy.deepcopy(base)
     arena_a, arena_b = adopt_module(base), adopt_module(lane)
@@ -107,13 +113,18 @@ def test_wgrad_second_stream_is_bit_identical():
             la = sa(x, y).item()
             K.set_wgrad_overlap(True)
             lb = sb(x, y).item()
-            assert la == lb
+            assert (la == lb) if same_splits else (abs(la - lb) <= 5e-2 * max(1.0, abs(la)))
         assert sb.replays >= 2 and arena_b.grads_in_place()
         torch.cuda.synchronize()
-        assert torch.equal(arena_a.param_buf, arena_b.param_buf)
-        assert torch.equal(arena_a.grad_buf, arena_b.grad_buf)
+        if same_splits:
+            assert torch.equal(arena_a.param_buf, arena_b.param_buf)
+            assert torch.equal(arena_a.grad_buf, arena_b.grad_buf)
+        else:  # different summation order, amplified by five training steps: close, not equal
+            assert torch.isfinite(arena_b.param_buf).all()
+            assert float((arena_a.param_buf - arena_b.param_buf).abs().max()) < 0.05
     finally:
-        K.set_wgrad_overlap(False)
+        K.set_wgrad_overlap(saved_overlap)
+        K.BWD_TARGET_CTAS = saved_target
 
 
 def test_eval_mode_and_metrics():

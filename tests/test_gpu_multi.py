@@ -30,7 +30,10 @@ def test_all_sync_modes_on_real_gpus():
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
            os.path.join(ROOT, "tools", "multi_gpu_check.py")]
-    proc = subprocess.run(cmd, capture_output=True, text=True, timeout=850)
+    env = dict(os.environ)
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    env["CHECK_OUT"] = os.path.join(ROOT, "gpurun_out", f"multi_gpu_check_{world}gpu.json")
+    proc = subprocess.run(cmd, capture_output=True, text=True, timeout=850, env=env)
     lines = [l for l in proc.stdout.splitlines() if l.startswith("MULTI_GPU_CHECK ")]
     assert proc.returncode == 0 and lines, (proc.stdout[-2000:], proc.stderr[-3000:])
     rep = json.loads(lines[-1][len("MULTI_GPU_CHECK "):])

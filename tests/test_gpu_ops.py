@@ -60,23 +60,70 @@ def test_linear_and_cross_entropy(K):
         assert torch.allclose(db.cpu(), b.grad, rtol=1e-4, atol=1e-6)
 
 
+def test_fused_head_forward_backward(K):
+    """Linear + cross-entropy as one forward and one backward launch against the CPU oracle (loss, logits, arg-max hits,
+    dx / dW / db including a non-unit upstream gradient); twice per size so the ticket counter must have re-armed."""
+    torch.manual_seed(5)
+    for B in (1, 7, 32, 80, 256):
+        for g in (1.0, 0.37):
+            x = torch.randn(B, 512, requires_grad=True)
+            w = (torch.randn(10, 512) * 0.05).requires_grad_(True)
+            b = torch.randn(10, requires_grad=True)
+            y = torch.randint(0, 10, (B,))
+            logits = F.linear(x, w, b)
+            loss = F.cross_entropy(logits, y)
+            (loss * g).backward()
+            xd, wd, bd, yd = x.detach().cuda(), w.detach().cuda(), b.detach().cuda(), y.cuda()
+            metrics = torch.zeros(2, device="cuda")
+            l, lg, dz = K.head_fwd(xd, wd, bd, yd, metrics)
+            assert torch.allclose(lg.cpu(), logits.detach(), rtol=1e-4, atol=1e-4)
+            assert torch.allclose(l.cpu(), loss.detach(), rtol=1e-5, atol=1e-5)
+            assert int(metrics[1].item()) == int((logits.argmax(1) == y).sum())
+            assert torch.allclose(metrics[0].cpu(), loss.detach(), rtol=1e-5, atol=1e-5)
+            dx, dw, db = torch.empty_like(xd), torch.empty_like(wd), torch.empty_like(bd)
+            K.head_bwd(dz, xd, wd, torch.full((), g, device="cuda"), dx, dw, db)
+            assert torch.allclose(dx.cpu(), x.grad, rtol=1e-4, atol=1e-6)
+            assert torch.allclose(dw.cpu(), w.grad, rtol=1e-4, atol=1e-5)
+            assert torch.allclose(db.cpu(), b.grad, rtol=1e-4, atol=1e-6)
+
+
 @pytest.mark.parametrize("N,C,H,pool", [(4, 64, 32, True), (8, 128, 16, True), (32, 512, 2, True), (8, 512, 4, False)])
-def test_bn_backward_cluster_kernel(K, N, C, H, pool):
-    """Same oracle through the one-launch cluster kernel (DSMEM exchange of the per-channel sums), enabled here for
-    layers of up to 8192 pixels (it is off by default)."""
+def test_bn_backward_separate_finalize_kernel(K, N, C, H, pool):
+    """Same oracle through the three-launch path (partial rows, finalize kernel, apply) that callers without
+    accumulators get."""
     from distributed_pytorch_b200 import _native
     lib = _native.require()
-    lib.dpb_set_tuning(9, 8192)
-    try:
-        assert lib.dpb_bn_bwd_launches(N, H, H, C, int(pool)) == (1 if N * H * H <= 8192 else 3)
-        test_bn_relu_pool_forward_backward(K, N, C, H, pool)
-    finally:
-        lib.dpb_set_tuning(9, 0)
+    assert lib.dpb_bn_bwd_launches(C, 0) == 3 and lib.dpb_bn_bwd_launches(C, 1) == 2
+    test_bn_relu_pool_forward_backward(K, N, C, H, pool, use_acc=False)
+
+
+@pytest.mark.parametrize("train", [True, False])
+def test_device_augmentation_matches_host_transform(K, train):
+    """The augmentation kernel (gather + RandomCrop(pad 4) + flip + Normalize) against the host transform of
+    data/datasets.py for the same indices: hashed draws, and explicit draws covering every corner of the crop range."""
+    import numpy as np
+    from distributed_pytorch_b200.data.datasets import augment_draws, synthetic_cifar10
+    ds = synthetic_cifar10(train, size=300, seed=3)
+    ds.set_epoch(2)
+    idx = np.array([5, 17, 0, 299, 123, 42, 42, 7, 250, 11, 1, 2, 3], dtype=np.int64)
+    images, labels = ds.to_device(torch.device("cuda"))
+    idx_dev = torch.from_numpy(idx.astype(np.int32)).cuda()
+    x, y = K.augment_batch(images, labels, idx_dev, train, ds.seed, ds.epoch)
+    xr, yr = ds.get_batch(idx)
+    assert torch.equal(y.cpu(), yr)
+    assert torch.allclose(x.cpu(), xr, rtol=0, atol=1e-6)
+    if train:
+        draws = augment_draws(idx, ds.seed, ds.epoch)
+        assert len({tuple(d) for d in draws.tolist()}) > 3  # the hash does vary
+        corner = np.array([[0, 0, 0], [8, 8, 1], [0, 8, 1], [8, 0, 0], [4, 4, 1]] * 3, dtype=np.int32)[:len(idx)]
+        x2, _ = K.augment_batch(images, labels, idx_dev, True, 0, 0, torch.from_numpy(corner).cuda())
+        xr2, _ = ds.get_batch(idx, corner)
+        assert torch.allclose(x2.cpu(), xr2, rtol=0, atol=1e-6)
 
 
 @pytest.mark.parametrize("N,C,H,pool", [(4, 64, 32, True), (3, 128, 16, True), (5, 256, 8, False), (32, 512, 2, True),
                                         (7, 512, 4, False)])
-def test_bn_relu_pool_forward_backward(K, N, C, H, pool):
+def test_bn_relu_pool_forward_backward(K, N, C, H, pool, use_acc=True):
     torch.manual_seed(2)
     y = torch.randn(N, C, H, H) * 1.5 + 0.3
     gamma = torch.rand(C) + 0.5
@@ -106,7 +153,11 @@ def test_bn_relu_pool_forward_backward(K, N, C, H, pool):
     assert torch.allclose(rmd.cpu(), rm, rtol=1e-4, atol=1e-5) and torch.allclose(rvd.cpu(), rv, rtol=1e-4, atol=1e-5)
     assert int(nbt.item()) == 1
     dg, db, dcb = torch.empty(C, device="cuda"), torch.empty(C, device="cuda"), torch.ones(C, device="cuda")
-    dy = K.bn_relu_pool_bwd(yd, nhwc(dout.cuda()), stats, gamma.cuda(), dg, db, dcb, pool)
+    dy = K.bn_relu_pool_bwd(yd, nhwc(dout.cuda()), stats, gamma.cuda(), dg, db, dcb, pool, use_acc=use_acc)
+    if use_acc:  # and once more: the apply pass must have cleared the accumulator slot it used
+        sc = K.scratch(yd.device)
+        torch.cuda.synchronize()
+        assert int(sc.bn_acc.abs().max().item()) == 0 and int(sc.bn_tickets.abs().max().item()) == 0
     scale = max(1.0, float(yr.grad.abs().max()))
     assert torch.allclose(dy.cpu(), yr.grad, rtol=2e-3, atol=2e-4 * scale)
     assert torch.allclose(dg.cpu(), g_.grad, rtol=2e-3, atol=2e-3)
@@ -144,6 +195,12 @@ def test_first_conv_fprop_and_wgrad(K, N, HW, tensor_cores):
     lib.dpb_set_tuning(7, tensor_cores)
     try:
         ps, pq, parts = K.first_conv_fprop(x.cuda(), wd, b.cuda(), y, True)
+        if K.first_conv_on_tensor_cores(HW, HW):  # the same statistics through the fixed-point accumulators
+            acc = torch.zeros(128, dtype=torch.int64, device="cuda")
+            K.first_conv_fprop(x.cuda(), wd, b.cuda(), torch.empty_like(y), False, stat_acc=acc)
+            ssum, ssq = K.acc_to_float(acc, 64)
+            assert torch.allclose(ssum.float(), ps.sum(0), rtol=1e-4, atol=1e-2)
+            assert torch.allclose(ssq.float(), pq.sum(0), rtol=1e-4, atol=1e-2)
         dw = torch.empty_like(wd)
         K.first_conv_wgrad(x.cuda(), nhwc(dy.cuda()), dw)
         torch.cuda.synchronize()

@@ -37,7 +37,7 @@ def one(mode, nt, splits, N, H, Cin, Cout):
     try:
         if mode == 0:
             out = K.nhwc_empty(N, Cout, H, H, "cuda"); out.fill_(float("nan"))
-            K.conv3x3_gemm(0, N, H, H, Cin, Cout, xd, None, wd, out, bd, want_stats=False, nt=nt, splits=splits)
+            K.conv3x3_gemm(0, N, H, H, Cin, Cout, xd, None, wd, out, bd, nt=nt, splits=splits)
             ref = y.detach()
         elif mode == 1:
             out = K.nhwc_empty(N, Cin, H, H, "cuda"); out.fill_(float("nan"))
@@ -87,9 +87,7 @@ def one(mode, nt, splits, N, H, Cin, Cout):
         res.update(ok=False, error=str(e)[:400])
         try:
             import ctypes
-            arr = (ctypes.c_int * 5)()
-            _native.require().dpb_last_device_error(arr)
-            res["device_error"] = list(arr)
+            res["device_error"] = _native.device_error_message()
         except Exception as e2:  # noqa: BLE001
             res["device_error"] = "unreadable: " + str(e2)[:100]
     print("RESULT " + json.dumps(res))

@@ -11,6 +11,8 @@ from distributed_pytorch_b200 import _native  # noqa: E402
 from distributed_pytorch_b200.ops import kernels as K  # noqa: E402
 
 batch = int(sys.argv[1]) if len(sys.argv) > 1 else 256
+os.environ["DPB_EXPERIMENTS"] = "1"
+_native.build(experiments=True)  # the in-kernel tracing is compiled in only with -DDPB_EXPERIMENTS
 lib = _native.require()
 dump = torch.zeros(16384, device="cuda")
 lib.dpb_debug_set_conv_dump(dump.data_ptr())
