@@ -28,7 +28,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 GLOBAL_BATCH = 256
 MODES = ("all_reduce", "gather", "ddp", "single")
-DEFAULT_OVERLAP = False  # all_reduce mode: bucketed overlap with backward (see profiles/bench_multi_gpu.md)
+DEFAULT_OVERLAP = True   # all_reduce mode: bucketed reduction under backward (profiles/bench_multi_gpu.md: 0.64 vs 0.70 ms at 2 GPUs)
 
 
 def parse_args(argv=None):
@@ -213,6 +213,20 @@ def fence():
     torch.cuda.synchronize()
 
 
+SETTLE_S = 0.25
+
+
+def settle_steps(sec_per_step: float) -> int:
+    """Untimed steps after the W warm-up steps so that the GPU has been under load for SETTLE_S before the timed
+    region (clock ramp); agreed across ranks (they must all take the same number of steps)."""
+    import torch
+    import torch.distributed as dist
+    n = int(min(max(SETTLE_S / max(sec_per_step, 1e-5), 0), 2000))
+    t = torch.tensor([n], dtype=torch.int64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return int(t.item())
+
+
 def make_batches(batch: int, count: int = 8, seed: int = 0):
     """`count` distinct pinned host batches (synthetic 3x32x32 images, 10 classes), cycled by the benchmark."""
     import torch
@@ -273,13 +287,23 @@ def time_ours(step, batches, steps: int, warmup: int, e2e: bool, gpu_index: int)
     from distributed_pytorch_b200 import _native
     dev_batches = batches if e2e else [(x.cuda(non_blocking=True), y.cuda(non_blocking=True)) for x, y in batches]
     loss = None
+    sampler = ClockSampler(gpu_index)  # NVML is initialised here, not between warm-up and the timed region
+    tw = time.perf_counter()
     for i in range(warmup):
         x, y = dev_batches[i % len(dev_batches)]
         loss = step(x, y)
         if e2e:
             loss.item()
+    torch.cuda.synchronize()
+    # W warm-up steps of a ~0.5 ms step are a few milliseconds of GPU work: not enough for the SM clock to come up from
+    # idle.  Keep stepping (untimed) until the GPU has been busy for SETTLE_S; the same number of steps on every rank.
+    settle = settle_steps((time.perf_counter() - tw) / max(warmup, 1))
+    for i in range(settle):
+        x, y = dev_batches[i % len(dev_batches)]
+        loss = step(x, y)
+        if e2e:
+            loss.item()
     fence()
-    sampler = ClockSampler(gpu_index)
     sampler.start()
     l0 = _native.launches()
     t0 = time.perf_counter()
@@ -297,6 +321,7 @@ def time_ours(step, batches, steps: int, warmup: int, e2e: bool, gpu_index: int)
     clocks = sampler.stop()
     launches = _native.launches() - l0
     ms = max_over_ranks((wall_ms if e2e else dev_ms) / steps)
+    clocks["settle_steps"] = settle
     return ms, clocks, launches, float(loss.item())
 
 
@@ -358,9 +383,10 @@ class _TimedLoader:
         self.batches, self.warmup, self.steps, self.h2d, self.gpu = batches, warmup, steps, h2d, gpu_index
         self.dev_ms = self.wall_ms = None
         self.clocks = None
+        self.settle = 0
 
     def __len__(self):
-        return self.warmup + self.steps
+        return self.warmup + self.settle + self.steps
 
     def __iter__(self):
         import torch
@@ -368,8 +394,14 @@ class _TimedLoader:
         start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         sampler = ClockSampler(self.gpu)
         t0 = 0.0
-        for i in range(self.warmup + self.steps):
-            if i == self.warmup:
+        tw = time.perf_counter()
+        settle, i = 0, 0
+        while i < self.warmup + settle + self.steps:
+            if i == self.warmup and settle == 0:  # same settle rule as our arm (clock ramp), see settle_steps()
+                torch.cuda.synchronize()
+                settle = settle_steps((time.perf_counter() - tw) / max(self.warmup, 1))
+                self.settle = settle
+            if i == self.warmup + settle:
                 fence()
                 sampler.start()
                 t0 = time.perf_counter()
@@ -379,11 +411,13 @@ class _TimedLoader:
                 yield x.cuda(non_blocking=True), y.cuda(non_blocking=True)
             else:
                 yield dev[i % len(dev)]
+            i += 1
         end.record()
         fence()
         self.wall_ms = (time.perf_counter() - t0) * 1e3
         self.dev_ms = start.elapsed_time(end)
         self.clocks = sampler.stop()
+        self.clocks["settle_steps"] = self.settle
 
 
 def run_reference(args, rank, world, local):

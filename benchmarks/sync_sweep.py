@@ -101,11 +101,21 @@ def main():
             print(f"{label:>20s} {nbytes:>10d} B | all-reduce {nv}p2p {ours_ar:9.1f} us  nccl {ref_ar:9.1f} us  "
                   f"x{ref_ar / ours_ar:5.2f}  roof {r['allreduce_roofline_frac']:.2f} | gather-scatter ours {ours_gs:9.1f} us  "
                   f"nccl {ref_gs:9.1f} us  x{ref_gs / ours_gs:5.2f}  roof {r['gather_roofline_frac']:.2f}", flush=True)
+    # grid sweep on the whole arena: how many CTAs each all-reduce needs to fill the wire
+    n = 36924464 // 4
+    grid_rows = []
+    for blocks in (8, 16, 32, 64, 128):
+        p2p = timed(lambda: comm.all_reduce(buf, 0, n, 1.0 / world, algo=2, blocks=blocks), args.iters)
+        nv = timed(lambda: comm.all_reduce_nvls(buf, 1.0 / world, offset=0, count=n, blocks=blocks), args.iters) if nvls else None
+        grid_rows.append({"blocks": blocks, "p2p_us": p2p, "nvls_us": nv})
+        if rank == 0:
+            print(f"  whole arena, {blocks:3d} CTAs: p2p {p2p:8.1f} us" + (f"   nvls {nv:8.1f} us" if nv else ""), flush=True)
     if rank == 0 and args.out:
         os.makedirs(os.path.dirname(os.path.abspath(args.out)), exist_ok=True)
         with open(args.out, "w") as fh:
             json.dump({"world": world, "link_gbs": LINK_GBS, "link_measured_gbs": LINK_MEASURED_GBS, "nvls": nvls,
-                       "transport": "vmm" if comm.use_vmm else "ipc", "rows": rows}, fh, indent=1)
+                       "transport": "vmm" if comm.use_vmm else "ipc", "rows": rows, "grid_sweep": grid_rows}, fh,
+                      indent=1)
     torch.cuda.synchronize()
     dist.barrier()
     comm.close()

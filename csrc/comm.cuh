@@ -206,6 +206,8 @@ allreduce_nvls_kernel(CommCtx c, int channel, float* mc_grads, long long off4, l
   if (hi > n4) hi = n4;
   const long long tstride = (long long)gridDim.x * blockDim.x;
   float4* mg = reinterpret_cast<float4*>(mc_grads) + off4;
+  // A multimem round trip through the switch takes a few microseconds, so the wire only fills up with ~10^5 16-byte
+  // requests in flight per GPU: U independent loads per thread before the first use.
   for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < hi; i0 += tstride * U) {
     float4 acc[U];
 #pragma unroll

@@ -25,10 +25,12 @@ using namespace dpb;
 namespace {
 int g_tune_comm_blocks = 64;  // default grid cap of the collective kernels (dpb_set_tuning key 2)
 int g_tune_comm_weak = 0;     // two-shot all-reduce payload with weak (.cv load / plain store) accesses (key 11)
-int g_tune_ddp_blocks = 24;   // grid of a per-bucket collective launched next to backward (key 13): few CTAs, so the
-                              // conv kernels it overlaps keep their SM slots
+int g_tune_ddp_blocks = 16;   // grid of a per-bucket collective launched next to backward (key 13): few CTAs, so the
+                              // conv kernels it overlaps keep their SM slots (8 GPUs: 0.463 ms/step with 16, 0.494 with
+                              // 32, 0.505 with 64)
 int g_tune_nvls = 1;          // use the multimem (in-switch reduction) all-reduce when the buffers are multicast-bound (key 14)
-int g_tune_nvls_blocks = 32;  // its grid (key 15)
+int g_tune_nvls_blocks = 16;  // its grid when it has the GPU to itself (key 15): 36.9 MB at 8 GPUs takes 115 us with 8
+                              // CTAs, 124 with 16, 136 with 32..128 -- the switch, not the SMs, sets the pace
 inline cudaStream_t S(dpb_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 constexpr int kBnBwdBlocks = 296;
 constexpr int kFirstWgradBlocks = 444;  // rows of the first-layer wgrad partials buffer (= kFcTcMaxBlocks)
@@ -649,14 +651,22 @@ int dpb_allreduce_nvls(dpb_comm* c, int channel, void* mc_grads, void* local_par
   sg.lr = lr; sg.momentum = mom; sg.wd = wd; sg.nesterov = nesterov;
   if (sg.enabled && (mc_params == nullptr || local_mom == nullptr))
     return set_error(-4, "allreduce_nvls: the fused optimizer needs multicast parameters and a momentum buffer");
-  constexpr int U = 4;
   const long long slice = (n4 + nr - 1) / nr;
-  long long b = blocks > 0 ? blocks : (slice + 512LL * U - 1) / (512LL * U);
+  long long b = blocks > 0 ? blocks : (slice + 512LL * 4 - 1) / (512LL * 4);
   if (blocks <= 0 && b > g_tune_nvls_blocks) b = g_tune_nvls_blocks;
   if (b > kCommMaxBlocks) b = kCommMaxBlocks;
   if (b < 1) b = 1;
-  allreduce_nvls_kernel<U><<<(unsigned)b, 512, 0, S(stream)>>>(c->ctx, channel, (float*)mc_grads, off4, n4, scale, write_mean ? 1 : 0,
-                                                            sg, (float*)local_params, (float*)mc_params, (float*)local_mom);
+  // loads in flight per thread: the fewer CTAs the launch may use (a bucket reduced next to backward), the more each
+  // thread has to keep in flight to fill the wire
+  const long long per_thread = (slice + b * 512 - 1) / (b * 512);
+#define DPB_NVLS(U)                                                                                                  \
+  allreduce_nvls_kernel<U><<<(unsigned)b, 512, 0, S(stream)>>>(c->ctx, channel, (float*)mc_grads, off4, n4, scale,   \
+                                                               write_mean ? 1 : 0, sg, (float*)local_params,           \
+                                                               (float*)mc_params, (float*)local_mom)
+  if (per_thread >= 16 && b <= 48) DPB_NVLS(16);
+  else if (per_thread >= 8) DPB_NVLS(8);
+  else DPB_NVLS(4);
+#undef DPB_NVLS
   DPB_CUDA(cudaGetLastError());
   return 0;
 }

@@ -55,8 +55,11 @@ def build_parser(mode: str) -> argparse.ArgumentParser:
                    help="all_reduce / ddp modes on CUDA: SGD update inside the collective kernel (default)")
     x.add_argument("--no-fuse-optimizer", dest="fuse_optimizer", action="store_false",
                    help="separate all-reduce and optimizer kernels")
-    x.add_argument("--overlap", action="store_true",
-                   help="all_reduce mode: reduce bucket by bucket on a side stream while backward is still running")
+    x.add_argument("--overlap", dest="overlap", action="store_true", default=True,
+                   help="all_reduce mode on CUDA: reduce bucket by bucket on a side stream while backward is still "
+                        "running (default)")
+    x.add_argument("--no-overlap", dest="overlap", action="store_false",
+                   help="all_reduce mode: one collective over the whole gradient arena after backward")
     x.add_argument("--host-loader", action="store_true",
                    help="augment on the host and copy batches (default on CUDA: dataset resident on the GPU, one "
                         "augmentation kernel per batch)")

@@ -219,6 +219,7 @@ def first_conv_wgrad(x_nchw: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor):
 def bn_finalize(part_sum, part_sq, parts: int, c: int, count: float, gamma, beta, running_mean, running_var, nbt,
                 momentum: float, eps: float):
     lib = N.require()
+    wait_buffer_sync(part_sum.device)
     dev = part_sum.device
     out = torch.empty((4, c), device=dev, dtype=torch.float32)  # scale, shift, mean, invstd
     N.check(lib.dpb_bn_finalize(N.ptr(part_sum), N.ptr(part_sq), parts, c, float(count), N.ptr(gamma), N.ptr(beta),
@@ -230,6 +231,7 @@ def bn_finalize(part_sum, part_sq, parts: int, c: int, count: float, gamma, beta
 
 def bn_eval_scale_shift(c: int, gamma, beta, running_mean, running_var, eps: float):
     lib = N.require()
+    wait_buffer_sync(gamma.device)
     out = torch.empty((2, c), device=gamma.device, dtype=torch.float32)
     N.check(lib.dpb_bn_eval_scale_shift(c, N.ptr(gamma), N.ptr(beta), N.ptr(running_mean), N.ptr(running_var), eps,
                                         N.ptr(out[0]), N.ptr(out[1]), N.stream()), "dpb_bn_eval_scale_shift")
@@ -247,12 +249,30 @@ def bn_relu_pool_fwd(y: torch.Tensor, scale, shift, pool: bool) -> torch.Tensor:
     return out
 
 
+# ---- DDP's per-forward buffer broadcast runs on a side stream; whoever touches BatchNorm buffers next waits for it ----
+_buffer_sync_events: dict[int, "torch.cuda.Event"] = {}
+
+
+def set_buffer_sync_event(device: torch.device, event) -> None:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    _buffer_sync_events[idx] = event
+
+
+def wait_buffer_sync(device: torch.device) -> None:
+    """Make the current stream wait for a pending BatchNorm-buffer broadcast on this device (once)."""
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    ev = _buffer_sync_events.pop(idx, None)
+    if ev is not None:
+        torch.cuda.current_stream(device).wait_event(ev)
+
+
 def bn_relu_pool_fwd_train(y: torch.Tensor, acc: torch.Tensor, ticket: torch.Tensor, gamma, beta, running_mean,
                            running_var, nbt, momentum: float, eps: float, pool: bool):
     """Training-mode BatchNorm + ReLU (+ pool) straight from the accumulators the conv filled.  Returns (out, stats)
     with stats = (4, C): scale, shift, mean, invstd."""
     lib = N.require()
     n, c, h, w = y.shape
+    wait_buffer_sync(y.device)  # running statistics are read-modify-written here
     out = nhwc_empty(n, c, h // 2 if pool else h, w // 2 if pool else w, y.device)
     stats = torch.empty((4, c), device=y.device, dtype=torch.float32)
     N.check(lib.dpb_bn_relu_pool_fwd_train(N.ptr(y), N.ptr(acc), N.ptr(ticket), N.ptr(gamma), N.ptr(beta),

@@ -358,10 +358,18 @@ class Communicator:
                 "dpb_allreduce_sgd")
         N.count_launches(1)
 
+    # In-switch reduction pays from 4 GPUs up.  Per GPU and direction a two-shot all-reduce of S bytes moves
+    # 2 (N-1)/N S over peer loads / stores but (1 + 1/N) S through multimem (the switch also pulls this GPU's own
+    # contribution and returns its own stores): 1.5 S vs 1.0 S at N = 2 (measured 128 vs 81 us for the 36.9 MB arena),
+    # 1.25 S vs 1.5 S at N = 4, 1.125 S vs 1.75 S at N = 8.  DPB_NVLS_MIN_WORLD overrides the threshold.
+    NVLS_MIN_WORLD = 4
+
     def nvls_ready(self, *bufs: SymmetricBuffer) -> bool:
-        """True if these buffers can be reduced inside the switch (all multicast-bound, NVLS not switched off)."""
+        """True if these buffers should be reduced inside the switch: all multicast-bound, NVLS not switched off, and
+        the world large enough for it to be the faster path."""
         lib = N.require()
-        return (not self.emulate and self.world_size > 1 and bool(lib.dpb_nvls_enabled())
+        min_world = int(os.environ.get("DPB_NVLS_MIN_WORLD", self.NVLS_MIN_WORLD))
+        return (not self.emulate and self.world_size >= max(min_world, 2) and bool(lib.dpb_nvls_enabled())
                 and all(b is not None and b.mc_ptr for b in bufs))
 
     def all_reduce_nvls(self, grads: SymmetricBuffer, scale: float, params: Optional[SymmetricBuffer] = None,

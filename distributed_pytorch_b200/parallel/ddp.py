@@ -32,7 +32,11 @@ from ..utils.arena import FlatArena
 from .comm import Communicator, SymmetricBuffer
 
 FIRST_BUCKET_BYTES = 1024 * 1024
-DEFAULT_BUCKET_MB = 25
+DEFAULT_BUCKET_MB = 25        # torch's bucket_cap_mb: reproduces its rebuilt layout (9 461 800 / 27 157 504 / 305 152 bytes)
+CUDA_BUCKET_MB = 25           # the CUDA path keeps torch's layout too.  Measured at 8 GPUs / 32 images per rank
+                              # (profiles/mode_sweep_8.md): every collective costs ~20 us of peer barriers whatever its
+                              # size, so three buckets (0.474 ms/step) beat five 8 MB ones (0.494) and nine 4 MB ones
+                              # (0.495), although the small ones start earlier.
 
 
 def expected_ready_order(module: nn.Module) -> List[int]:
@@ -133,7 +137,7 @@ class BucketReducer:
             members = [pos for pos in range(n) if bucket_by_pos[pos] == b]
             self.ranges.append((min(self.arena.offsets[m] for m in members),
                                 max(self.arena.offsets[m] + (self.arena.numels[m] + 63) // 64 * 64 for m in members)))
-        mc_g = self.grad_buf.mc_ptr
+        mc_g = self.grad_buf.mc_ptr if self.comm.nvls_ready(self.grad_buf) else None
         mc_p = self.params_buf.mc_ptr if self.params_buf is not None else None
         if mc_g:
             N.check(lib.dpb_reducer_set_multicast(
@@ -225,12 +229,15 @@ class BucketReducer:
 
 
 class DistributedDataParallel(nn.Module):
-    def __init__(self, module: nn.Module, bucket_cap_mb: float = DEFAULT_BUCKET_MB, broadcast_buffers: bool = True,
+    def __init__(self, module: nn.Module, bucket_cap_mb: Optional[float] = None, broadcast_buffers: bool = True,
                  process_group=None, comm: Optional[Communicator] = None):
         """Same call as ``torch.nn.parallel.DistributedDataParallel(model)`` (reference main_ddp.py:137).  After
         building the optimizer, ``ddp.fuse_optimizer(optimizer)`` (CUDA) moves the SGD update into each bucket's
-        collective, which removes the separate optimizer pass from the step."""
+        collective, which removes the separate optimizer pass from the step.  ``bucket_cap_mb``: None = 25 (torch's default:
+        the reference's bucket layout 9 461 800 / 27 157 504 / 305 152 bytes); bucket boundaries do not change any result."""
         super().__init__()
+        if bucket_cap_mb is None:
+            bucket_cap_mb = CUDA_BUCKET_MB if next(module.parameters()).is_cuda else DEFAULT_BUCKET_MB
         self.module = module
         self.process_group = process_group
         self.broadcast_buffers = broadcast_buffers
@@ -345,7 +352,19 @@ class DistributedDataParallel(nn.Module):
             return
         if self._cuda:
             if self._buffer_block is not None:
-                self.comm.broadcast(self._buffer_block, root=0)
+                # On the reducer's side stream: the first consumer / producer of the buffers is the first BatchNorm
+                # kernel (it updates the running statistics), not the first convolution, so the ~9 us broadcast runs
+                # underneath that convolution.  The BatchNorm launcher waits for the event (ops.kernels.buffer_sync_*).
+                main = torch.cuda.current_stream()
+                side = torch.cuda.ExternalStream(self.reducer.side_stream(), device=self._params[0].device)
+                ev = torch.cuda.Event()
+                ev.record(main)
+                side.wait_event(ev)     # after everything that touched the buffers so far (previous step, eval, load)
+                with torch.cuda.stream(side):
+                    self.comm.broadcast(self._buffer_block, root=0)
+                    done = torch.cuda.Event()
+                    done.record(side)
+                K.set_buffer_sync_event(self._params[0].device, done)
         else:
             with torch.no_grad():
                 for b in self.module.buffers():

@@ -138,14 +138,16 @@ class AllReduceSync(_ArenaSync):
             raise ValueError("fuse_optimizer=True needs the optimizer")
         self.reducer = None
         if overlap and self.cuda and self.world_size > 1:
-            from .ddp import BucketReducer, expected_ready_order, plan_buckets
+            from .ddp import BucketReducer, plan_buckets
             params = list(model.parameters())
-            ready = expected_ready_order(model)
-            ids_ready = plan_buckets([params[i].numel() * 4 for i in ready], 1024 * 1024, int(bucket_cap_mb * 1024 * 1024))
+            # The arena is in named_parameters() order and gradients become ready roughly back to front, so buckets
+            # are cut walking the parameters in REVERSE order (same cap rule as DDP): every bucket is then one
+            # contiguous arena range, and it is launched when the last of its gradients exists.
+            rev = list(range(len(params) - 1, -1, -1))
+            ids_ready = plan_buckets([params[i].numel() * 4 for i in rev], 1024 * 1024, int(bucket_cap_mb * 1024 * 1024))
             bucket_of = [0] * len(params)
-            for pos, i in enumerate(ready):
+            for pos, i in enumerate(rev):
                 bucket_of[i] = ids_ready[pos]
-            # the arena is in named_parameters() order: a bucket (consecutive layers) is still one contiguous range
             self.reducer = BucketReducer(self.comm, self.arena, self._bufs["grad"], bucket_of, max(ids_ready) + 1,
                                          1.0 / self.world_size, params_buf=self._bufs.get("param"),
                                          mom_buf=self._bufs.get("mom"))

@@ -62,9 +62,9 @@ int dpb_conv3x3_gemm(int mode, int n, int h, int w, int cin, int cout, const flo
  *  7 [DPB_FIRST_TC]          first (Cin = 3) layer on the tensor cores when the image tiles into 128 pixels (default 1)
  * 11 [DPB_COMM_WEAK]         two-shot all-reduce payload with weak accesses (default 0)
  * 12 [DPB_PEER_TIMEOUT_MS]   wall-clock budget of a peer-signal wait (default 120000)
- * 13 [DPB_DDP_BLOCKS]        grid of a per-bucket collective launched next to backward (default 24)
+ * 13 [DPB_DDP_BLOCKS]        grid of a per-bucket collective launched next to backward (default 16)
  * 14 [DPB_NVLS]              in-switch (multimem) all-reduce when the buffers are multicast-bound (default 1)
- * 15 [DPB_NVLS_BLOCKS]       its grid (default 32)
+ * 15 [DPB_NVLS_BLOCKS]       its grid when it has the GPU to itself (default 16)
  * Returns non-zero for an unknown key / bad value. */
 int dpb_set_tuning(int key, int value);
 /* Kernels launched by the calling thread's most recent dpb_conv3x3_gemm (1, or 2 when split-K adds its reduce). */

@@ -32,14 +32,15 @@ def _world():
 
 
 def _check_output(out: str, what: str):
-    losses = [float(x) for x in re.findall(r"Epoch: 1, Iteration: \d+-\d+, Average Loss: (\d+\.\d{3})", out)]
-    assert len(losses) >= 2, (what, out[-1500:])
-    assert re.search(r"Epoch: 1, Iteration: 1-20, Average Loss: \d+\.\d{3}", out), (what, out[-1500:])
-    assert re.search(r"Epoch: 1, Iteration: 21-40, Average Loss: \d+\.\d{3}", out), (what, out[-1500:])
+    # (under torchrun the ranks share one stdout, so a window's line appears once per rank)
+    first = [float(x) for x in re.findall(r"Epoch: 1, Iteration: 1-20, Average Loss: (\d+\.\d{3})", out)]
+    second = [float(x) for x in re.findall(r"Epoch: 1, Iteration: 21-40, Average Loss: (\d+\.\d{3})", out)]
+    assert first and len(first) == len(second), (what, out[-1500:])
+    losses = [sum(first) / len(first), sum(second) / len(second)]
     m = re.search(r"Avg Time for iteration 2-40: ([\d.e-]+) seconds\.", out)
     assert m, (what, out[-1500:])
     assert re.search(r"Test set: Average loss: \d+\.\d{4}, Accuracy: \d+/\d+ \(\d+%\)", out), (what, out[-1500:])
-    assert all(l == l and l < 50 for l in losses), (what, losses)
+    assert all(l == l and l < 50 for l in first + second), (what, first, second)
     assert losses[1] < losses[0], (what, "loss did not fall", losses)
     return float(m.group(1))
 
@@ -94,7 +95,7 @@ def test_main_single_process(tmp_path, ref_model_module):
 @pytest.mark.timeout(1200)
 @pytest.mark.parametrize("script,extra", [("main_gather.py", []), ("main_all_reduce.py", []),
                                           ("main_all_reduce.py", ["--no-fuse-optimizer"]),
-                                          ("main_all_reduce.py", ["--overlap"]), ("main_part3.py", []),
+                                          ("main_all_reduce.py", ["--no-overlap"]), ("main_part3.py", []),
                                           ("main_part3.py", ["--no-fuse-optimizer"])])
 def test_flag_launched_modes(tmp_path, ref_model_module, script, extra):
     world = _world()
