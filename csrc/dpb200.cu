@@ -679,7 +679,9 @@ int dpb_allreduce(dpb_comm* c, int channel, void* const* bufs, long long offset,
   if (count == 0) return 0;
   const long long n4 = count / 4;
   constexpr int U = 4;
-  if (algo == 0) algo = (n4 * 16 <= (256 << 10)) ? 1 : 2;  // <= 256 KiB: one-shot
+  // one-shot (every rank pulls everything) only for the tiniest messages: measured at 8 GPUs it costs 41-62 us from
+  // 16 KiB to 256 KiB while the two-shot kernel moves 1 MiB in 29 us (profiles/sync_sweep_8.md)
+  if (algo == 0) algo = (n4 * 16 <= (8 << 10)) ? 1 : 2;
   if (algo == 1) {
     int b = (int)((n4 + 512LL * U - 1) / (512LL * U));
     if (b <= comm_block_cap(c, allreduce_oneshot_kernel<true, U>, 512)) {  // the whole range must fit one grid pass

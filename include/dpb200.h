@@ -137,7 +137,8 @@ int dpb_bn_plain_bwd(const float* x, const float* dout, const float* save_mean, 
 /* Allocation-free variant of dpb_bn_relu_pool_bwd.  (No counterpart in the reference: it exists for callers of this
  * library that cannot obtain device memory themselves -- a host program that talks only to this C ABI, or a plug-in
  * that is given input/output buffers and must not call cudaMalloc or any framework allocator.)
- * Same arguments and results as dpb_bn_relu_pool_bwd minus `part` and `coef`: that scratch lives in a file-scope
+ * Same arguments and results as dpb_bn_relu_pool_bwd minus its scratch arguments (`part`, `coef`, and the optional
+ * `acc` / `ticket`; it always takes the three-launch path): that scratch lives in a file-scope
  * __device__ array inside the library (about 1.2 MB on every GPU that loads it, held until the process exits).
  *   - limit: c <= dpb_noalloc_max_channels() (512); larger c is refused with an error, nothing is launched.
  *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress) with that device

@@ -9,8 +9,9 @@ import subprocess
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "distributed_pytorch_b200", "_lib", "libdpb200.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-FULL = {"conv_gemm_kernel<0, 128, 3, 1, 1>": "conv_gemm_fprop_nt128.sass",
-        "conv_gemm_kernel<2, 128, 3, 1, 1>": "conv_gemm_wgrad_nt128.sass",
+FULL = {"conv_gemm_kernel<0, 128, 3, true>": "conv_gemm_fprop_nt128_cluster.sass",
+        "conv_gemm_kernel<2, 128, 3, false>": "conv_gemm_wgrad_nt128.sass",
+        "allreduce_nvls_kernel<16>": "allreduce_nvls.sass",
         "first_conv_fprop_tc_kernel": "first_conv_fprop_tc.sass",
         "first_conv_wgrad_tc_kernel": "first_conv_wgrad_tc.sass",
         "allreduce_twoshot_kernel<false, 8, 2>": "allreduce_twoshot_8ranks.sass"}
@@ -30,7 +31,8 @@ def main():
     for part in re.split(r"\n\s*Function : ", txt)[1:]:
         funcs[part.split("\n", 1)[0].strip()] = part
     key = re.compile(r"\b(UTC[A-Z0-9]*MMA[A-Z0-9_.]*|UTMALDG[A-Z0-9_.]*|UTMAPF[A-Z0-9_.]*|LDTM[A-Z0-9_.]*|UTCBAR[A-Z0-9_.]*|"
-                     r"SYNCS[A-Z0-9_.]*|HMMA[A-Z0-9_.]*|ELECT[A-Z0-9_.]*|UCGABAR[A-Z0-9_.]*)\b")
+                     r"SYNCS[A-Z0-9_.]*|HMMA[A-Z0-9_.]*|ELECT[A-Z0-9_.]*|UCGABAR[A-Z0-9_.]*|LDGMC[A-Z0-9_.]*|STGMC[A-Z0-9_.]*|REDGMC[A-Z0-9_.]*|"
+                     r"LDS[A-Z0-9_.]*CLUSTER[A-Z0-9_.]*|MAPA[A-Z0-9_.]*|ATOMG[A-Z0-9_.]*|RED[A-Z0-9_.]*64[A-Z0-9_.]*)\b")
     sysop = re.compile(r"\b((?:LDG|STG|LD|ST)\.E[A-Z0-9_.]*SYS[A-Z0-9_.]*|MEMBAR\.[A-Z.]*SYS[A-Z.]*)")
     rows = []
     for name, body in funcs.items():
@@ -48,7 +50,7 @@ def main():
         fh.write("# SASS evidence (cuobjdump -sass libdpb200.so, sm_100a)\n\n"
                  "Per kernel: instruction count, the Blackwell tensor/TMA/mbarrier mnemonics (`UTC*MMA` = tcgen05.mma, `UTMALDG` = "
                  "cp.async.bulk.tensor, `LDTM` = tcgen05.ld, `UTCBAR` = tcgen05.commit, `SYNCS` = mbarrier, `UCGABAR` = cluster "
-                 "barrier) and system-scope memory operations (NVLink peer loads/stores and flags).  No `HMMA` (legacy mma.sync) "
+                 "barrier, `LDGMC.E.ADD.F32` = multimem.ld_reduce, the in-switch NVLS load-reduce) and system-scope memory operations (NVLink peer loads/stores and flags).  No `HMMA` (legacy mma.sync) "
                  "anywhere.\n\n| kernel | instrs | tcgen05 / TMA / mbarrier | system-scope (peer) ops |\n|---|---|---|---|\n")
         for d, n, tc, so in rows:
             fh.write(f"| `{d}` | {n} | {', '.join(f'{k} x{v}' for k, v in sorted(tc.items())) or '-'} | "

@@ -19,16 +19,14 @@ import distributed_pytorch_b200 as dpb  # noqa: E402
 from distributed_pytorch_b200 import _native  # noqa: E402
 
 VARIANTS = [  # name, mode, kwargs
-    ("all_reduce", "all_reduce", dict(overlap=False)),
+    ("all_reduce (one collective after backward)", "all_reduce", dict(overlap=False)),
     ("all_reduce overlap cap25 b16", "all_reduce", dict(overlap=True, cap=25, blocks=16)),
-    ("all_reduce overlap cap25 b8", "all_reduce", dict(overlap=True, cap=25, blocks=8)),
     ("all_reduce overlap cap25 b16 p2p", "all_reduce", dict(overlap=True, cap=25, blocks=16, nvls=False)),
-    ("all_reduce overlap cap16 b16", "all_reduce", dict(overlap=True, cap=16, blocks=16)),
-    ("all_reduce overlap cap12 b16", "all_reduce", dict(overlap=True, cap=12, blocks=16)),
+    ("all_reduce overlap cap25 b8", "all_reduce", dict(overlap=True, cap=25, blocks=8)),
+    ("all_reduce overlap cap25 b24", "all_reduce", dict(overlap=True, cap=25, blocks=24)),
     ("ddp cap25 b16", "ddp", dict(cap=25, blocks=16)),
-    ("ddp cap25 b8", "ddp", dict(cap=25, blocks=8)),
     ("ddp cap25 b16 p2p", "ddp", dict(cap=25, blocks=16, nvls=False)),
-    ("ddp cap12 b16", "ddp", dict(cap=12, blocks=16)),
+    ("ddp cap25 b8", "ddp", dict(cap=25, blocks=8)),
     ("ddp cap25 b16 unfused", "ddp", dict(cap=25, blocks=16, fuse=False)),
     ("gather", "gather", dict()),
 ]

@@ -12,16 +12,17 @@ OUT=${GRAFT_REPO_ROOT:-.}/gpurun_out
 mkdir -p "$OUT"
 LOG=$OUT/sanitizer_$TOOL.log
 SUM=$OUT/sanitizer_$TOOL.txt
-TESTS="tests/test_gpu_conv.py::test_conv_tiles_and_split_k[128-1] tests/test_gpu_conv.py::test_conv_tiles_and_split_k[128-8] \
-tests/test_gpu_conv.py::test_conv_tiles_and_split_k[64-16] tests/test_gpu_conv.py::test_conv_tiles_and_split_k[128-3] \
-tests/test_gpu_conv.py::test_conv_fprop_with_batchnorm_statistics[8-4-256-512-0-1] \
-tests/test_gpu_ops.py::test_fused_head_forward_backward tests/test_gpu_ops.py::test_bn_relu_pool_forward_backward \
-tests/test_gpu_ops.py::test_first_conv_fprop_and_wgrad[8-32-1] tests/test_gpu_comm.py::test_allreduce_oneshot_twoshot_and_gather[4]"
+TESTS="tests/test_gpu_conv.py tests/test_gpu_ops.py tests/test_gpu_comm.py"
+# one case per code path: unsplit, cluster split-K (DSMEM reduce), workspace split-K, conv -> BatchNorm through the
+# accumulators, fused head, BatchNorm backward (both paths), first layer on the tensor cores, emulated-rank collectives
+SELECT="test_conv_tiles_and_split_k and (128-1 or 128-8 or 64-16 or 128-3) or test_conv_then_batchnorm_from_accumulators and 8-4-256-512 \
+or test_fused_head_forward_backward or test_bn_relu_pool_forward_backward and 32-512-2 or test_bn_backward_separate_finalize_kernel and 8-128-16 \
+or test_first_conv_fprop_and_wgrad and 8-32-1 or test_allreduce_oneshot_twoshot_and_gather and 4"
 EXTRA=""
 [ "$TOOL" = "racecheck" ] && EXTRA="--racecheck-report all"
 echo "compute-sanitizer --tool $TOOL $EXTRA : $(date -u)" > "$SUM"
 timeout 3000 compute-sanitizer --tool "$TOOL" $EXTRA --error-exitcode 99 --print-limit 30 \
-  python -m pytest $TESTS -x -q -p no:cacheprovider > "$LOG" 2>&1
+  python -m pytest $TESTS -k "$SELECT" -x -q -p no:cacheprovider > "$LOG" 2>&1
 RC=$?
 echo "exit code: $RC" >> "$SUM"
 grep -E "ERROR SUMMARY|RACECHECK SUMMARY|passed|failed|error" "$LOG" | tail -20 >> "$SUM"
