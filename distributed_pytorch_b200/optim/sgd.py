@@ -68,16 +68,17 @@ class SGD(Optimizer):
 
     @staticmethod
     def _arena_of(group):
-        """The arena if this group is exactly one arena's parameters, in order, with in-place gradients."""
+        """The arena if this group is exactly one arena's parameters with in-place gradients."""
         ps = group["params"]
         if not ps:
             return None
         arena = getattr(ps[0], "_dpb_arena", None)
         if arena is None or len(ps) != len(arena.params):
             return None
-        for a, b in zip(ps, arena.params):
-            if a is not b:
-                return None
+        # the same set of parameters in any order (DDP lays its arena out in gradient-ready order): the update is
+        # elementwise, so one launch over the whole arena is the same thing
+        if {id(p) for p in ps} != {id(p) for p in arena.params}:
+            return None
         return arena if arena.grads_in_place() else None
 
     @torch.no_grad()

@@ -144,9 +144,10 @@ class BucketReducer:
                 self._handle, mc_g, mc_p, self.params_buf.tensor.data_ptr() if self.params_buf is not None else None,
                 self.mom_buf.tensor.data_ptr() if self.mom_buf is not None else None), "dpb_reducer_set_multicast")
         self._pos_of_param = {i: pos for i, pos in enumerate(pos_of)}
-        for i, p in enumerate(self._params):
-            if p.requires_grad:
-                p.register_post_accumulate_grad_hook(self._make_hook(i))
+        if self.comm.world_size > 1:  # a world of one has nothing to reduce: no hooks, the optimizer does its own step
+            for i, p in enumerate(self._params):
+                if p.requires_grad:
+                    p.register_post_accumulate_grad_hook(self._make_hook(i))
         if optimizer is not None:
             self.fuse_optimizer(optimizer)
         self.prepare()
@@ -156,6 +157,8 @@ class BucketReducer:
         """From now on every bucket's collective also applies ``optimizer``'s SGD update to the bucket's parameters."""
         if self.params_buf is None or self.mom_buf is None:
             raise RuntimeError("fusing the optimizer needs symmetric parameter and momentum arenas")
+        if self.comm.world_size == 1:
+            return
         self._optimizer = optimizer
         self._push_hyper()
 

@@ -104,6 +104,8 @@ class GatherScatterSync(_ArenaSync):
     def sync(self) -> None:
         if self.cuda:
             self.arena.ensure_grads_in_place()
+            if self.world_size == 1:
+                return  # the mean over one rank is the gradient itself
             self.comm.gather_mean_scatter(self._bufs["grad"], 0, self.arena.total, 1.0 / self.world_size, root=0)
             return
         # CPU oracle: reference main_gather.py:42-59
@@ -132,7 +134,7 @@ class AllReduceSync(_ArenaSync):
         -- nothing in the reference's loop (main_all_reduce.py:45-48) depends on the order in which parameters are
         reduced, only on the result."""
         super().__init__(model, world_size, rank, comm, group, symmetric_params=fuse_optimizer)
-        self.fuses_optimizer = bool(fuse_optimizer and self.cuda)
+        self.fuses_optimizer = bool(fuse_optimizer and self.cuda and self.world_size > 1)
         self.optimizer = optimizer
         if self.fuses_optimizer and optimizer is None:
             raise ValueError("fuse_optimizer=True needs the optimizer")
@@ -169,6 +171,8 @@ class AllReduceSync(_ArenaSync):
                     self.optimizer.skip_next_step = True
                 return
             self.arena.ensure_grads_in_place()
+            if self.world_size == 1:
+                return  # nothing to average: optimizer.step() runs the plain fused SGD kernel over the arena
             scale = 1.0 / self.world_size
             if self.fuses_optimizer:
                 g = self.optimizer.param_groups[0]
