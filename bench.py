@@ -297,12 +297,19 @@ def time_ours(step, batches, steps: int, warmup: int, e2e: bool, gpu_index: int)
     torch.cuda.synchronize()
     # W warm-up steps of a ~0.5 ms step are a few milliseconds of GPU work: not enough for the SM clock to come up from
     # idle.  Keep stepping (untimed) until the GPU has been busy for SETTLE_S; the same number of steps on every rank.
-    settle = settle_steps((time.perf_counter() - tw) / max(warmup, 1))
-    for i in range(settle):
-        x, y = dev_batches[i % len(dev_batches)]
-        loss = step(x, y)
-        if e2e:
-            loss.item()
+    # (decided chunk by chunk: the warm-up steps include eager runs and the graph capture, so their average says nothing
+    # about how long a replayed step takes)
+    settle, ts = 0, time.perf_counter()
+    while settle < 4000:
+        for i in range(25):
+            x, y = dev_batches[i % len(dev_batches)]
+            loss = step(x, y)
+            if e2e:
+                loss.item()
+        settle += 25
+        torch.cuda.synchronize()
+        if max_over_ranks(time.perf_counter() - ts) >= SETTLE_S:  # the same decision on every rank
+            break
     fence()
     sampler.start()
     l0 = _native.launches()
