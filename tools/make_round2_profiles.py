@@ -56,7 +56,8 @@ def mode_sweeps():
              "per-bucket collective, `p2p` = NVLS switched off.", ""]
     for path in sorted(glob.glob(os.path.join(RAW, "mode_sweep_*.json"))):
         d = load(path)
-        lines += [f"## {d['world']} GPUs, {d['per_rank_batch']} images per rank", "",
+        tag = " (final defaults, second box)" if "final" in os.path.basename(path) else ""
+        lines += [f"## {d['world']} GPUs, {d['per_rank_batch']} images per rank{tag}", "",
                   "| variant | NVLS | min ms/step | median | images/s |", "|---|---|---|---|---|"]
         for r in d["rows"]:
             lines.append(f"| {r['variant']} | {'yes' if r['nvls'] else 'no'} | {r['ms_min']:.4f} | {r['ms_median']:.4f} | "
