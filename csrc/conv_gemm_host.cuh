@@ -168,6 +168,9 @@ inline int g_tune_min_k_iters = 8;  // k-iterations (of 32) a split must keep; f
 // kernel instead.  8 is the measured optimum (profiles/step_variants.md): 16-CTA clusters do not pack onto the GPCs --
 // of 256 CTAs 32 start a whole kernel-life late.
 inline int g_tune_cluster_max = 8;
+// A GEMM that wants up to cluster_max * reach / 2 splits still takes the cluster path (with cluster_max splits and
+// correspondingly longer K loops); beyond that it goes through the workspace with as many splits as it wants.
+inline int g_tune_cluster_reach = 3;
 
 struct SplitPlan {
   int splits;
@@ -195,7 +198,7 @@ inline SplitPlan plan_splits(int tiles, int m_tiles, int k_iters, int nt, int fo
     if (forced <= 0 && want * 2 >= s * 3 && s * 2 <= g_tune_cluster_max && s * 2 * 4 <= k_iters) s *= 2;
     // forced: only an exact power of two goes to the cluster path (tests pick the path by the number they force);
     // heuristic: the cluster path unless the GEMM wants far more splits than a cluster holds (early-layer wgrad)
-    const bool take = forced > 0 ? (s == want) : (want * 2 <= g_tune_cluster_max * 3);
+    const bool take = forced > 0 ? (s == want) : (want * 2 <= g_tune_cluster_max * g_tune_cluster_reach);
     if (take) {
       sp.splits = s;
       sp.cluster = true;

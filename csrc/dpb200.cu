@@ -132,6 +132,7 @@ int dpb_set_tuning(int key, int value) {
   }
   if (key == 13 && value >= 1 && value <= kCommMaxBlocks) { g_tune_ddp_blocks = value; return 0; }
   if (key == 14) { g_tune_nvls = value ? 1 : 0; return 0; }
+  if (key == 16 && value >= 2 && value <= 64) { g_tune_cluster_reach = value; return 0; }
   if (key == 15 && value >= 1 && value <= kCommMaxBlocks) { g_tune_nvls_blocks = value; return 0; }
   return set_error(-30, "dpb_set_tuning: bad key/value %d/%d", key, value);
 }

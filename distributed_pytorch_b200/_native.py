@@ -196,7 +196,7 @@ _SIGNATURES = {
 # dpb_set_tuning keys and the environment variables that set them at load time (include/dpb200.h)
 TUNING_ENV = ((0, "DPB_CONV_TARGET_CTAS"), (1, "DPB_CONV_NT"), (2, "DPB_COMM_BLOCKS"), (3, "DPB_CONV_MIN_K_ITERS"),
               (4, "DPB_PDL"), (5, "DPB_CONV_CLUSTER_MAX"), (7, "DPB_FIRST_TC"), (11, "DPB_COMM_WEAK"),
-              (13, "DPB_DDP_BLOCKS"), (14, "DPB_NVLS"), (15, "DPB_NVLS_BLOCKS"))
+              (13, "DPB_DDP_BLOCKS"), (14, "DPB_NVLS"), (15, "DPB_NVLS_BLOCKS"), (16, "DPB_CONV_CLUSTER_REACH"))
 
 
 def _bind(lib: ctypes.CDLL) -> None:

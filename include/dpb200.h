@@ -65,6 +65,7 @@ int dpb_conv3x3_gemm(int mode, int n, int h, int w, int cin, int cout, const flo
  * 13 [DPB_DDP_BLOCKS]        grid of a per-bucket collective launched next to backward (default 16)
  * 14 [DPB_NVLS]              in-switch (multimem) all-reduce when the buffers are multicast-bound (default 1)
  * 15 [DPB_NVLS_BLOCKS]       its grid when it has the GPU to itself (default 16)
+ * 16 [DPB_CONV_CLUSTER_REACH] a GEMM wanting up to cluster_max * reach / 2 splits still takes the cluster path (default 3)
  * Returns non-zero for an unknown key / bad value. */
 int dpb_set_tuning(int key, int value);
 /* Kernels launched by the calling thread's most recent dpb_conv3x3_gemm (1, or 2 when split-K adds its reduce). */
