@@ -74,6 +74,20 @@ def plan_buckets(bytes_in_ready_order: List[int], first_cap: int = FIRST_BUCKET_
     return ids
 
 
+def plan_reverse_buckets(bytes_in_named_order: List[int], first_cap: int = FIRST_BUCKET_BYTES,
+                         cap: int = DEFAULT_BUCKET_MB * 1024 * 1024) -> List[int]:
+    """Bucket id per parameter (``named_parameters()`` order) for an arena laid out in that order: the DDP cap rule applied
+    walking the parameters back to front -- gradients become ready roughly in that order -- so that every bucket is one
+    contiguous arena range.  (Cutting in true gradient-ready order would split a layer's conv.weight / conv.bias /
+    bn.weight / bn.bias across two buckets whose ranges then interleave.)"""
+    n = len(bytes_in_named_order)
+    ids_rev = plan_buckets(list(reversed(bytes_in_named_order)), first_cap, cap)
+    out = [0] * n
+    for pos, b in enumerate(ids_rev):
+        out[n - 1 - pos] = b
+    return out
+
+
 def gather_sharded_momentum(comm: Communicator, mom_buf: SymmetricBuffer, ranges) -> None:
     """Momentum of a range lives on the rank that owns the corresponding slice of the two-shot all-reduce (slice r of
     ``ceil(n4 / world)`` float4s); broadcast every slice from its owner."""

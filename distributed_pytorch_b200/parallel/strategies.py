@@ -8,9 +8,10 @@ strategy          reference                               here (CUDA)
 ``GatherScatter`` main_gather.py:42-59, 34x gather +      ONE kernel: rank 0 pulls every peer's gradient arena
                   stack + mean + scatter, serial          over NVLink, reduces in rank order, x1/N in registers,
                                                           pushes the mean back with peer stores
-``AllReduce``     main_all_reduce.py:45-48, 34x           ONE kernel over the arena: one-shot / two-shot P2P
-                  all_reduce(SUM) + ``/= N``              all-reduce with the 1/N folded in; optionally the SGD
-                                                          update fused into the reduce-scatter epilogue
+``AllReduce``     main_all_reduce.py:45-48, 34x           two-shot all-reduce over the arena -- in-switch (NVLS
+                  all_reduce(SUM) + ``/= N``              multimem) from 4 GPUs, peer loads / stores otherwise -- with
+                                                          the 1/N and the SGD update fused in; by default cut into
+                                                          buckets that are reduced while backward is still running
 ================  ======================================  ==================================================
 
 (Bucketed DDP lives in :mod:`distributed_pytorch_b200.parallel.ddp`.)
@@ -140,17 +141,12 @@ class AllReduceSync(_ArenaSync):
             raise ValueError("fuse_optimizer=True needs the optimizer")
         self.reducer = None
         if overlap and self.cuda and self.world_size > 1:
-            from .ddp import BucketReducer, plan_buckets
+            from .ddp import BucketReducer, plan_reverse_buckets
             params = list(model.parameters())
-            # The arena is in named_parameters() order and gradients become ready roughly back to front, so buckets
-            # are cut walking the parameters in REVERSE order (same cap rule as DDP): every bucket is then one
-            # contiguous arena range, and it is launched when the last of its gradients exists.
-            rev = list(range(len(params) - 1, -1, -1))
-            ids_ready = plan_buckets([params[i].numel() * 4 for i in rev], 1024 * 1024, int(bucket_cap_mb * 1024 * 1024))
-            bucket_of = [0] * len(params)
-            for pos, i in enumerate(rev):
-                bucket_of[i] = ids_ready[pos]
-            self.reducer = BucketReducer(self.comm, self.arena, self._bufs["grad"], bucket_of, max(ids_ready) + 1,
+            # the arena is in named_parameters() order: buckets are cut back to front so each is one contiguous range
+            bucket_of = plan_reverse_buckets([p.numel() * 4 for p in params], 1024 * 1024,
+                                             int(bucket_cap_mb * 1024 * 1024))
+            self.reducer = BucketReducer(self.comm, self.arena, self._bufs["grad"], bucket_of, max(bucket_of) + 1,
                                          1.0 / self.world_size, params_buf=self._bufs.get("param"),
                                          mom_buf=self._bufs.get("mom"))
             self.reducer.attach(params, optimizer if self.fuses_optimizer else None)

@@ -59,3 +59,18 @@ def test_ready_order_and_bucket_layout_match_reference_ddp():
     assert members[0] == [33, 32, 30, 31, 28]
     assert members[2] == [9, 6, 7, 4, 5, 2, 3, 0, 1]
     assert plan_buckets([100], 1 << 20, 25 << 20) == [0]
+
+
+def test_reverse_bucket_plan_gives_contiguous_arena_ranges():
+    """all_reduce mode with overlap keeps its arena in named_parameters() order; its buckets (cut back to front) must
+    each cover one contiguous run of parameters, for every cap, or the reducer's arena ranges would interleave."""
+    import distributed_pytorch_b200 as dpb
+    from distributed_pytorch_b200.parallel.ddp import plan_reverse_buckets
+    for name in ("VGG11", "VGG19"):
+        sizes = [p.numel() * 4 for p in dpb.VGG(name).parameters()]
+        for cap_mb in (1, 4, 8, 10, 25, 1000):
+            ids = plan_reverse_buckets(sizes, 1 << 20, cap_mb << 20)
+            assert len(ids) == len(sizes) and ids[-1] == 0          # the last parameter is in the first-ready bucket
+            assert all(a >= b for a, b in zip(ids, ids[1:]))          # monotone => every bucket is one contiguous run
+            assert sorted(set(ids)) == list(range(max(ids) + 1))
+        assert max(plan_reverse_buckets(sizes, 1 << 20, 1000 << 20)) <= 1
